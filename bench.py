@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py -- SpMV GNNZ/s (+ algorithmic HBM GB/s vs roofline) on 1/2/4/8 B200.
+
+A "step" is one pass of the hot path (y += A*x, software/SoftwareSpMV.cpp:59-64) over the
+whole matrix.  Default workload = BASELINE.json configs[2]: synthetic uniform-random
+16M x 16M, 32 nnz/row, fp64.  N > 1: the same matrix split into nnz-balanced row blocks, one
+rank per GPU, no data-path collective ("strong" scaling; value = total nnz / max-over-ranks time).
+
+  python bench.py [--gpus N --steps K --warmup W] [--workload uniform|rmat|banded-power]
+  python bench.py --impl reference ...   # the reference's own CPU loop on a bounded sample
+
+Python/torch here is plumbing (rendezvous, pinned buffers); the timed work is libb200spmv.so.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "spmv-vector-cache_b200"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+SEED = 0x5EED5EED
+METRIC = "SpMV GNNZ/s"
+WORKLOADS = {
+    # name: (kind, rows, nnz_per_row, description)
+    "uniform": (0, 1 << 24, 32, "synthetic uniform-random 16M x 16M, 32 nnz/row, fp64"),
+    "rmat": (1, 1 << 26, 32, "synthetic R-MAT scale 26 (64M rows, 2^31 nnz), fp64"),
+    "banded-power": (2, 1 << 27, 5, "power iteration, 128M-row banded(11)+5 random, fp64"),
+}
+
+
+def b_alg(nnz, rows, cols):
+    """values + u32 indices + u32 pointers + x read once + y written once."""
+    return 12 * nnz + 4 * (rows + 1) + 8 * cols + 8 * rows
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi-equivalent clock / throttle-reason samples via NVML during the timed region."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40,
+                 "sw_thermal_slowdown": 0x20, "hw_power_brake": 0x80, "sync_boost": 0x10}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def start(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def cpu_reference_sample(steps, warmup):
+    """The reference's CPU loop on a bounded sample of the headline workload: the same
+    16M x 16M uniform shape (same 134 MB x / y footprints, so the random read-modify-write of y
+    that dominates SoftwareSpMV.cpp:62 misses cache the same way) at 2 nnz/row = 1/16 of the nnz.
+    Uses oracle/_ref (the unmodified reference, kind "reference") when present, else the port."""
+    import numpy as np
+    import helpers as H
+    oracle = H.OracleLib()
+    rows = cols = 1 << 24
+    npr = 2
+    colptr, rowind, vals = oracle.synth_csc(0, SEED, rows, cols, npr, "f64")
+    x = oracle.synth_x(SEED + 1, cols, "f64")
+    y = np.zeros(rows)
+    nnz = int(rowind.size)
+    use_ref = H.RefLib.available()
+    ref = H.RefLib() if use_ref else None
+    times = []
+    budget_s, t_begin = 90.0, time.perf_counter()
+    for i in range(warmup + steps):
+        if i > warmup + 2 and time.perf_counter() - t_begin > budget_s:
+            break  # bounded: keep the whole arm within a few minutes whatever K is
+        y[:] = 0.0
+        if use_ref:
+            t = ref.spmv("f64", rows, cols, colptr, rowind, vals, x, y)  # loop-only bracket, SoftwareSpMV.cpp:57,66
+        else:
+            t0 = time.perf_counter()
+            oracle.spmv_csc("f64", rows, cols, colptr, rowind, vals, x, y)
+            t = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(t)
+    tot = sum(times)
+    return {
+        "value": nnz * len(times) / tot / 1e9, "unit": "GNNZ/s", "cores": 1,
+        "kind": "reference" if use_ref else "port",
+        "sample": "uniform 16M x 16M at %d nnz/row (%d nnz = 1/16 of the workload, same x/y footprint), "
+                  "%d timed SpMV, single thread (the reference loop is single-threaded), host has %d cores"
+                  % (npr, nnz, len(times), os.cpu_count()),
+        "ms_per_step": 1e3 * tot / len(times), "nnz": nnz, "rows": rows, "cols": cols, "steps": len(times),
+    }
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    warmup = min(args.warmup, 3)
+    r = cpu_reference_sample(args.steps, warmup)
+    steps = r["steps"]
+    kind, rows, npr, desc = WORKLOADS["uniform"]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": "GNNZ/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "sample": r["sample"]},
+        "cpu_baseline": {"value": r["value"], "unit": "GNNZ/s", "cores": 1, "kind": r["kind"], "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": "GNNZ/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gb_s_algorithmic": b_alg(r["nnz"], r["rows"], r["cols"]) / (r["ms_per_step"] * 1e-3) / 1e9,
+    }
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import b200spmv as b2
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    kind, rows, npr, desc = WORKLOADS[args.workload]
+    if args.rows:
+        rows = args.rows
+    cols = rows
+    flags = 0 if args.overwrite else b2.ACCUMULATE
+    if args.no_persist:
+        flags |= b2.NO_PERSIST
+
+    eng = b2.Engine(local)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(b2.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        eng.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
+    if args.slabs:
+        eng.set_option("slabs", args.slabs)
+    t0 = time.perf_counter()
+    eng.setup_synthetic(kind, rows, cols, npr, SEED, b2.F64)
+    setup_s = time.perf_counter() - t0
+    nnz, lnnz, lrows = eng.stat("nz"), eng.stat("local_nz"), eng.stat("local_rows")
+    eng.fill_x_synthetic(SEED + 1)
+    eng.fill_y_zero()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    power = args.workload == "banded-power"
+    sampler = ClockSampler(local)
+    # ---- device-resident timing: W warm-up, then exactly K steps --------------------------
+    if power:
+        eng.power_iterate(max(args.warmup, 3), False, flags & ~b2.ACCUMULATE)
+    else:
+        eng.exec_device(max(args.warmup, 3), flags)
+    barrier()
+    launches0 = eng.stat("launches")
+    sampler.start()
+    if power:
+        ms_total, _ = eng.power_iterate(args.steps, True, flags & ~b2.ACCUMULATE)
+    else:
+        ms = eng.exec_device(args.steps, flags)  # CUDA events on the launching stream, one pair per step
+        ms_total = float(ms.sum())
+    barrier()
+    launches = eng.stat("launches") - launches0
+    t_dev = max_over_ranks(ms_total) * 1e-3
+    value = nnz * args.steps / t_dev / 1e9
+
+    # ---- the dominant kernel alone (roofline), same workload, events around each launch ----
+    eng.set_option("profile", 1)
+    eng.exec_device(args.steps, flags)
+    k_ns, k_n = eng.stat("merge_kernel_ns"), eng.stat("merge_kernel_launches")
+    eng.set_option("profile", 0)
+    slabs = eng.stat("slabs")
+    kernel_ms_per_step = k_ns * 1e-6 / max(1, k_n) * slabs
+    peak, peak_src = measured_peak_gbs()
+    alg_local = 12 * lnnz + 4 * (lrows + 1) + 8 * cols + 8 * lrows
+    achieved = alg_local / (kernel_ms_per_step * 1e-3) / 1e9
+
+    # ---- end to end through b200spmv_exec with pinned HOST vectors --------------------------
+    dt = torch.float64
+    xh = torch.empty(cols, dtype=dt).pin_memory()
+    yh = torch.zeros(rows, dtype=dt).pin_memory()
+    xh.copy_(torch.from_numpy(eng.get_x()))
+    e2e_steps = min(args.steps, 50)
+    for _ in range(3):
+        eng.exec(xh.data_ptr(), yh.data_ptr(), flags)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        eng.exec(xh.data_ptr(), yh.data_ptr(), flags)  # H2D x (+y), kernels, D2H y; blocking
+    torch.cuda.synchronize()
+    t_e2e = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    clocks = sampler.stop()
+    h2d = 8 * cols + (8 * lrows if flags & b2.ACCUMULATE else 0)
+    d2h = 8 * lrows
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "GNNZ/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": desc, "rows": rows, "cols": cols, "nnz": nnz, "seed": SEED,
+                       "semantics": "y = A*x" if args.overwrite else "y += A*x (reference semantics)",
+                       "partition": "nnz-balanced row blocks, no collective" if not power else
+                                    "row blocks + x all-gather per step",
+                       "l2": "inputs (%.1f GB) larger than L2; no flush" % (b_alg(nnz, rows, cols) / 1e9),
+                       "slabs": slabs, "persist_window": not args.no_persist, "setup_s": round(setup_s, 2)},
+            "gb_s_algorithmic": b_alg(nnz, rows, cols) * args.steps / t_dev / 1e9 if world == 1 else None,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "spmv_merge_kernel", "kernel_ms_per_step": kernel_ms_per_step,
+                         "algorithmic_bytes_per_step": alg_local, "frac_of_8TBs_nominal": achieved / 8000.0},
+            "e2e": {"value": nnz * e2e_steps / t_e2e / 1e9, "unit": "GNNZ/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": 1e3 * t_e2e / e2e_steps},
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu:
+            r = cpu_reference_sample(3, 1)
+            line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="uniform", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="override the row count (experiments only)")
+    ap.add_argument("--slabs", type=int, default=0)
+    ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
+    ap.add_argument("--no-persist", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -167,16 +167,17 @@ ORACLE_API uint32_t oracle_max_alive(uint32_t rows, uint32_t nnz, uint32_t *inds
 }
 
 /* SparseMatrix::maxColSpan, SparseMatrix.cpp:110-119: max over columns of        */
-/* inds[last]-inds[first] in unsigned arithmetic on the raw (unmasked) words.     */
-/* The reference reads inds[colptr[c+1]-1] even for an empty column; so do we      */
-/* (an empty column 0 would read inds[-1]; callers avoid that case, as the         */
-/* reference's own callers do -- guarded here to stay memory-safe).                */
-ORACLE_API uint32_t oracle_max_col_span(uint32_t cols, const uint32_t *colptr,
+/* inds[colptr[c+1]-1] - inds[colptr[c]] in unsigned arithmetic on the raw words.  */
+/* Like the reference, an EMPTY interior column is not skipped (it compares the    */
+/* neighbouring columns' entries).  Only reads that would leave the array -- an    */
+/* empty leading column (colptr[c+1]==0) or trailing one (colptr[c]==nnz) -- are   */
+/* skipped, for memory safety; the reference's callers never hit them.             */
+ORACLE_API uint32_t oracle_max_col_span(uint32_t cols, uint32_t nnz, const uint32_t *colptr,
                                         const uint32_t *inds)
 {
     uint32_t best = 0;
     for (uint32_t c = 0; c < cols; c++) {
-        if (colptr[c + 1] == 0) continue; /* memory-safety guard only */
+        if (colptr[c + 1] == 0 || colptr[c] >= nnz) continue; /* memory-safety guard only */
         uint32_t span = inds[colptr[c + 1] - 1] - inds[colptr[c]];
         if (span > best) best = span;
     }

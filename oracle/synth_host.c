@@ -69,3 +69,31 @@ ORACLE_API void synth_host_coo_to_compressed(uint32_t nkeys, uint64_t nnz, const
     }
     free(cur);
 }
+
+/* y[r] of y = A*x for ONE row of a row-generated synthetic matrix with the synthetic x
+ * (synth_x_bits(xseed, col)), summed in CSR = reference order with separate mul and add.
+ * Lets a test spot-check rows of a matrix far too large to materialise on the host. */
+ORACLE_API uint64_t synth_host_row_dot(int kind, uint64_t seed, uint32_t r, uint32_t rows, uint32_t cols,
+                                       uint32_t npr, int dtype_u64, uint64_t xseed, double *abs_sum)
+{
+    uint32_t c[SYNTH_MAX_NPR + 2 * SYNTH_BAND_HALF + 1];
+    uint64_t v[SYNTH_MAX_NPR + 2 * SYNTH_BAND_HALF + 1];
+    uint32_t n = synth_gen_row(kind, seed, r, rows, cols, npr, dtype_u64, c, v);
+    if (dtype_u64) {
+        uint64_t acc = 0;
+        for (uint32_t k = 0; k < n; k++) acc += v[k] * synth_x_bits(xseed, c[k], 1);
+        return acc;
+    }
+    union { double d; uint64_t u; } a, b, out;
+    double acc = 0.0, mag = 0.0;
+    for (uint32_t k = 0; k < n; k++) {
+        a.u = v[k];
+        b.u = synth_x_bits(xseed, c[k], 0);
+        double prod = a.d * b.d;
+        acc += prod;
+        mag += prod < 0 ? -prod : prod;
+    }
+    if (abs_sum) *abs_sum = mag;
+    out.d = acc;
+    return out.u;
+}

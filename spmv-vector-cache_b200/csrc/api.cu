@@ -1,0 +1,367 @@
+// api.cu -- the C ABI of include/b200spmv.h: lifetime, setup (upload + device transpose),
+// exec, vectors, statistics.  Multi-GPU entry points are in multi.cu.
+#include <algorithm>
+#include <chrono>
+#include <vector>
+
+#include "common.cuh"
+
+static std::string g_create_error;
+
+static uint64_t now_ns()
+{
+    return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(
+               std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+static void release_matrix(b200spmv_ctx *ctx)
+{
+    DeviceCsr &m = ctx->csr;
+    b2_free(m.rowptr); b2_free(m.colind);
+    { uint64_t *v = (uint64_t *)m.vals; b2_free(v); m.vals = nullptr; }
+    b2_free(m.tile_row); b2_free(m.tile_nz); b2_free(m.carry_row);
+    { uint64_t *v = (uint64_t *)m.carry_val; b2_free(v); m.carry_val = nullptr; }
+    b2_free(ctx->csc_colptr); b2_free(ctx->csc_rowind);
+    { uint64_t *v = (uint64_t *)ctx->csc_vals; b2_free(v); ctx->csc_vals = nullptr; }
+    { uint64_t *v = (uint64_t *)ctx->d_x; b2_free(v); ctx->d_x = nullptr; }
+    { uint64_t *v = (uint64_t *)ctx->d_y; b2_free(v); ctx->d_y = nullptr; }
+    ctx->ready = false;
+}
+
+extern "C" int b200spmv_create(b200spmv_ctx **out, int device)
+{
+    if (!out) return B200SPMV_EINVAL;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                         " (there is no CPU fallback in this library)";
+        return B200SPMV_ECUDA;
+    }
+    if (device < 0 || device >= ndev) { g_create_error = "device index out of range"; return B200SPMV_EINVAL; }
+    b200spmv_ctx *ctx = new b200spmv_ctx();
+    ctx->device = device;
+    cudaDeviceProp prop;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) {
+        g_create_error = cudaGetErrorString(e);
+        delete ctx;
+        return B200SPMV_ECUDA;
+    }
+    ctx->sms = prop.multiProcessorCount;
+    ctx->l2_bytes = (size_t)prop.l2CacheSize;
+    ctx->max_persist_bytes = (size_t)prop.persistingL2CacheMaxSize;
+    // reserve the largest L2 set-aside the device offers for persisting lines: the "vector cache"
+    if (ctx->max_persist_bytes) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, ctx->max_persist_bytes);
+    *out = ctx;
+    return 0;
+}
+
+extern "C" void b200spmv_destroy(b200spmv_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    b2_comm_destroy(ctx);
+    release_matrix(ctx);
+    if (ctx->pin_x) cudaFreeHost(ctx->pin_x);
+    if (ctx->pin_y) cudaFreeHost(ctx->pin_y);
+    if (ctx->d_norm) cudaFree(ctx->d_norm);
+    free(ctx->h_row_splits);
+    cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream); cudaStreamDestroy(ctx->copy_stream);
+    delete ctx;
+}
+
+extern "C" const char *b200spmv_last_error(const b200spmv_ctx *ctx)
+{
+    return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t value)
+{
+    if (!ctx || !key) return B200SPMV_EINVAL;
+    const std::string k(key);
+    if (k == "slabs") { if (value < 0 || value > 64) return b2_fail(ctx, B200SPMV_EINVAL, "slabs must be 0..64"); ctx->opt_slabs = (int)value; }
+    else if (k == "persist_bytes") ctx->opt_persist_bytes = value;
+    else if (k == "require_aligned") ctx->opt_require_aligned = (int)value;
+    else if (k == "keep_csc") ctx->opt_keep_csc = (int)value;
+    else if (k == "profile") { ctx->opt_profile = (int)value; ctx->merge_kernel_ns = 0; ctx->merge_kernel_launches = 0; ctx->prof_n = 0; }
+    else return b2_fail(ctx, B200SPMV_EINVAL, "unknown option");
+    return 0;
+}
+
+// number of column slabs: x slice of one slab should sit in L2 next to the streams
+static int choose_slabs(const b200spmv_ctx *ctx)
+{
+    if (ctx->opt_slabs > 0) return ctx->opt_slabs;
+    const double xbytes = 8.0 * ctx->cols;
+    const double l2 = (double)ctx->l2_bytes;
+    if (l2 <= 0 || xbytes <= 0.6 * l2) return 1;
+    return std::min(64, (int)std::ceil(xbytes / (0.45 * l2)));
+}
+
+// ctx->csc_* (rank-local entries, global ids) -> slab-major CSR + merge-path tiles + vectors
+static int csc_to_csr(b200spmv_ctx *ctx, uint32_t index_mask)
+{
+    cudaStream_t s = ctx->stream;
+    DeviceCsr &m = ctx->csr;
+    const uint64_t t0 = now_ns();
+    ctx->slabs = choose_slabs(ctx);
+    ctx->slab_cols = (uint32_t)(((uint64_t)b2_div_up(ctx->cols, ctx->slabs) + 31) & ~31ull);
+    ctx->slabs = (int)b2_div_up(ctx->cols, ctx->slab_cols);
+    ctx->rowptr_stride = ((size_t)ctx->local_rows + 1 + 3) & ~(size_t)3;
+    B2_TRY(b2_alloc(ctx, &m.rowptr, ctx->rowptr_stride * ctx->slabs));
+    B2_TRY(b2_alloc(ctx, &m.colind, ctx->local_nnz));
+    { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->local_nnz)); m.vals = v; }
+    // zero the pad so over-reads past the last entry see column 0 / value 0
+    B2_CHECK(ctx, cudaMemsetAsync(m.colind + ctx->local_nnz, 0, 256, s));
+    B2_CHECK(ctx, cudaMemsetAsync((uint64_t *)m.vals + ctx->local_nnz, 0, 256, s));
+    for (int sl = 0; sl < ctx->slabs; sl++) {
+        const uint32_t c0 = (uint32_t)std::min<uint64_t>((uint64_t)sl * ctx->slab_cols, ctx->cols);
+        const uint32_t c1 = (uint32_t)std::min<uint64_t>((uint64_t)c0 + ctx->slab_cols, ctx->cols);
+        uint32_t e0 = 0, e1 = 0;
+        B2_CHECK(ctx, cudaMemcpy(&e0, ctx->csc_colptr + c0, 4, cudaMemcpyDeviceToHost));
+        B2_CHECK(ctx, cudaMemcpy(&e1, ctx->csc_colptr + c1, 4, cudaMemcpyDeviceToHost));
+        B2_TRY(b2_compress(ctx, ctx->local_rows, (uint64_t)e1 - e0, ctx->csc_rowind + e0, index_mask, ctx->row_begin,
+                           ctx->csc_colptr, ctx->cols, e0, nullptr, (const uint64_t *)ctx->csc_vals + e0,
+                           m.rowptr + sl * ctx->rowptr_stride, e0, m.colind + e0, (uint64_t *)m.vals + e0, s));
+    }
+    B2_CHECK(ctx, cudaStreamSynchronize(s));
+    ctx->transposetime_ns = now_ns() - t0;
+    if (!ctx->opt_keep_csc) {
+        b2_free(ctx->csc_colptr); b2_free(ctx->csc_rowind);
+        uint64_t *v = (uint64_t *)ctx->csc_vals; b2_free(v); ctx->csc_vals = nullptr;
+    }
+    B2_TRY(b2_build_tiles(ctx));
+    { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->cols)); ctx->d_x = v; }
+    { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->rows)); ctx->d_y = v; }
+    B2_CHECK(ctx, cudaMemsetAsync(ctx->d_x, 0, (size_t)ctx->cols * 8, s));
+    B2_CHECK(ctx, cudaMemsetAsync(ctx->d_y, 0, (size_t)ctx->rows * 8, s));
+    B2_CHECK(ctx, cudaStreamSynchronize(s));
+    ctx->persist_set = false;
+    ctx->ready = true;
+    return 0;
+}
+
+static bool aligned64(const void *p) { return ((uintptr_t)p & 63) == 0; }
+
+extern "C" int b200spmv_setup_csc(b200spmv_ctx *ctx, uint32_t rows, uint32_t cols, uint32_t nnz,
+                                  const uint32_t *colptr, const uint32_t *rowind, const void *vals,
+                                  int dtype, uint32_t index_mask)
+{
+    if (!ctx) return B200SPMV_EINVAL;
+    // SparseMatrix::fromMemory rejects zero dimensions (software/SparseMatrix.cpp:33-38)
+    if (rows == 0 || cols == 0 || nnz == 0) return b2_fail(ctx, B200SPMV_EINVAL, "matrix data is invalid (zero rows, cols or nz)");
+    if (!colptr || !rowind || !vals) return b2_fail(ctx, B200SPMV_EINVAL, "null matrix array");
+    if (dtype != B200SPMV_F64 && dtype != B200SPMV_U64) return b2_fail(ctx, B200SPMV_EINVAL, "dtype must be F64 or U64");
+    if (ctx->opt_require_aligned && !(aligned64(colptr) && aligned64(rowind) && aligned64(vals)))
+        return b2_fail(ctx, B200SPMV_EALIGN, "matrix arrays must be 64-byte aligned (HardwareSpMV.cpp:6-16)");
+    if (colptr[0] != 0 || colptr[cols] != nnz) return b2_fail(ctx, B200SPMV_EINVAL, "colptr[0] != 0 or colptr[cols] != nnz");
+    B2_CHECK(ctx, cudaSetDevice(ctx->device));
+    const uint64_t t0 = now_ns();
+    release_matrix(ctx);
+    ctx->dtype = dtype; ctx->rows = rows; ctx->cols = cols; ctx->nnz = nnz;
+    cudaStream_t s = ctx->stream;
+
+    // upload the whole CSC, then (when sharded) keep this rank's nnz-balanced row block
+    uint32_t *d_colptr = nullptr, *d_rowind = nullptr; uint64_t *d_vals = nullptr;
+    B2_TRY(b2_alloc(ctx, &d_colptr, (size_t)cols + 1));
+    B2_TRY(b2_alloc(ctx, &d_rowind, (size_t)nnz));
+    B2_TRY(b2_alloc(ctx, &d_vals, (size_t)nnz));
+    B2_CHECK(ctx, cudaMemcpyAsync(d_colptr, colptr, ((size_t)cols + 1) * 4, cudaMemcpyHostToDevice, s));
+    B2_CHECK(ctx, cudaMemcpyAsync(d_rowind, rowind, (size_t)nnz * 4, cudaMemcpyHostToDevice, s));
+    B2_CHECK(ctx, cudaMemcpyAsync(d_vals, vals, (size_t)nnz * 8, cudaMemcpyHostToDevice, s));
+    B2_CHECK(ctx, cudaStreamSynchronize(s));
+    ctx->csc_colptr = d_colptr; ctx->csc_rowind = d_rowind; ctx->csc_vals = d_vals;
+    ctx->row_begin = 0; ctx->row_end = rows; ctx->local_rows = rows; ctx->local_nnz = nnz;
+    if (ctx->world > 1) B2_TRY(b2_shard_csc(ctx, index_mask));
+    B2_TRY(csc_to_csr(ctx, index_mask));
+    ctx->setuptime_ns = now_ns() - t0;
+    return 0;
+}
+
+extern "C" int b200spmv_setup_synthetic(b200spmv_ctx *ctx, int kind, uint32_t rows, uint32_t cols,
+                                        uint32_t nnz_per_row, uint64_t seed, int dtype)
+{
+    if (!ctx) return B200SPMV_EINVAL;
+    if (rows == 0 || cols == 0 || nnz_per_row == 0) return b2_fail(ctx, B200SPMV_EINVAL, "matrix data is invalid (zero rows, cols or nz)");
+    if (dtype != B200SPMV_F64 && dtype != B200SPMV_U64) return b2_fail(ctx, B200SPMV_EINVAL, "dtype must be F64 or U64");
+    B2_CHECK(ctx, cudaSetDevice(ctx->device));
+    const uint64_t t0 = now_ns();
+    release_matrix(ctx);
+    ctx->dtype = dtype; ctx->rows = rows; ctx->cols = cols;
+    B2_TRY(b2_synth_build_csc(ctx, kind, nnz_per_row, seed));
+    B2_TRY(csc_to_csr(ctx, 0xFFFFFFFFu));
+    ctx->setuptime_ns = now_ns() - t0;
+    return 0;
+}
+
+// ---- exec -----------------------------------------------------------------------------------
+
+extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host, int flags)
+{
+    if (!ctx) return B200SPMV_EINVAL;
+    if (!ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "exec before setup");
+    if (!x_host || !y_host) return b2_fail(ctx, B200SPMV_EINVAL, "null vector");
+    if (ctx->opt_require_aligned && !(aligned64(x_host) && aligned64(y_host)))
+        return b2_fail(ctx, B200SPMV_EALIGN, "x and y must be 64-byte aligned (HardwareSpMV.cpp:14-15)");
+    B2_CHECK(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    const uint64_t t0 = now_ns();
+    uint64_t *yh = (uint64_t *)y_host + ctx->row_begin;
+    uint64_t *yd = (uint64_t *)ctx->d_y + ctx->row_begin;
+    B2_CHECK(ctx, cudaMemcpyAsync(ctx->d_x, x_host, (size_t)ctx->cols * 8, cudaMemcpyHostToDevice, s));
+    if (flags & B200SPMV_ACCUMULATE)
+        B2_CHECK(ctx, cudaMemcpyAsync(yd, yh, (size_t)ctx->local_rows * 8, cudaMemcpyHostToDevice, s));
+    B2_CHECK(ctx, cudaEventRecord(ctx->ev0, s));
+    B2_TRY(b2_spmv_launch(ctx, flags, s));
+    B2_CHECK(ctx, cudaEventRecord(ctx->ev1, s));
+    B2_CHECK(ctx, cudaMemcpyAsync(yh, yd, (size_t)ctx->local_rows * 8, cudaMemcpyDeviceToHost, s));
+    B2_CHECK(ctx, cudaStreamSynchronize(s));
+    float ms = 0.f;
+    B2_CHECK(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->spmvtime_ns = (uint64_t)((double)ms * 1e6);
+    const uint64_t total = now_ns() - t0;
+    ctx->xfertime_ns = total > ctx->spmvtime_ns ? total - ctx->spmvtime_ns : 0;
+    return 0;
+}
+
+extern "C" int b200spmv_exec_device(b200spmv_ctx *ctx, int iters, int flags, float *ms_each)
+{
+    if (!ctx || iters < 1) return B200SPMV_EINVAL;
+    if (!ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "exec before setup");
+    B2_CHECK(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    std::vector<cudaEvent_t> ev((size_t)iters + 1);
+    for (auto &e : ev) B2_CHECK(ctx, cudaEventCreate(&e));
+    int rc = 0;
+    cudaEventRecord(ev[0], s);
+    for (int i = 0; i < iters && rc == 0; i++) {
+        if (ctx->opt_profile && ctx->prof_n + 2 * ctx->slabs > 128) { cudaStreamSynchronize(s); b2_profile_collect(ctx); }
+        rc = b2_spmv_launch(ctx, flags, s);
+        cudaEventRecord(ev[i + 1], s);
+    }
+    cudaError_t e = cudaStreamSynchronize(s);
+    if (rc == 0 && e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; rc = B200SPMV_ECUDA; }
+    if (rc == 0) {
+        float last = 0.f;
+        for (int i = 0; i < iters; i++) {
+            cudaEventElapsedTime(&last, ev[i], ev[i + 1]);
+            if (ms_each) ms_each[i] = last;
+        }
+        ctx->spmvtime_ns = (uint64_t)((double)last * 1e6);
+    }
+    for (auto &x : ev) cudaEventDestroy(x);
+    return rc;
+}
+
+#define B2_NEED_READY(ctx)                                                       \
+    if (!(ctx)) return B200SPMV_EINVAL;                                          \
+    if (!(ctx)->ready) return b2_fail((ctx), B200SPMV_ESTATE, "call before setup"); \
+    B2_CHECK((ctx), cudaSetDevice((ctx)->device));
+
+extern "C" int b200spmv_set_x(b200spmv_ctx *ctx, const void *x_host)
+{
+    B2_NEED_READY(ctx);
+    B2_CHECK(ctx, cudaMemcpy(ctx->d_x, x_host, (size_t)ctx->cols * 8, cudaMemcpyHostToDevice));
+    return 0;
+}
+extern "C" int b200spmv_set_y(b200spmv_ctx *ctx, const void *y_host)
+{
+    B2_NEED_READY(ctx);
+    B2_CHECK(ctx, cudaMemcpy(ctx->d_y, y_host, (size_t)ctx->rows * 8, cudaMemcpyHostToDevice));
+    return 0;
+}
+extern "C" int b200spmv_fill_x_synthetic(b200spmv_ctx *ctx, uint64_t seed)
+{
+    B2_NEED_READY(ctx);
+    return b2_synth_fill_x(ctx, seed);
+}
+extern "C" int b200spmv_fill_y_zero(b200spmv_ctx *ctx)
+{
+    B2_NEED_READY(ctx);
+    B2_CHECK(ctx, cudaMemset(ctx->d_y, 0, (size_t)ctx->rows * 8));
+    return 0;
+}
+extern "C" int b200spmv_get_x(b200spmv_ctx *ctx, void *x_host)
+{
+    B2_NEED_READY(ctx);
+    B2_CHECK(ctx, cudaMemcpy(x_host, ctx->d_x, (size_t)ctx->cols * 8, cudaMemcpyDeviceToHost));
+    return 0;
+}
+extern "C" int b200spmv_get_y(b200spmv_ctx *ctx, void *y_host)
+{
+    B2_NEED_READY(ctx);
+    B2_CHECK(ctx, cudaMemcpy((uint64_t *)y_host + ctx->row_begin, (uint64_t *)ctx->d_y + ctx->row_begin,
+                             (size_t)ctx->local_rows * 8, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+// CSR of this rank's rows in ORIGINAL column order (slabs re-interleaved): rowptr[local_rows+1]
+// relative to the rank's first entry, colind/vals[local_nnz].
+extern "C" int b200spmv_get_csr(b200spmv_ctx *ctx, uint32_t *rowptr, uint32_t *colind, void *vals)
+{
+    B2_NEED_READY(ctx);
+    const size_t st = ctx->rowptr_stride;
+    std::vector<uint32_t> rp(st * ctx->slabs), ci(ctx->local_nnz);
+    std::vector<uint64_t> v(ctx->local_nnz);
+    B2_CHECK(ctx, cudaMemcpy(rp.data(), ctx->csr.rowptr, rp.size() * 4, cudaMemcpyDeviceToHost));
+    B2_CHECK(ctx, cudaMemcpy(ci.data(), ctx->csr.colind, ci.size() * 4, cudaMemcpyDeviceToHost));
+    B2_CHECK(ctx, cudaMemcpy(v.data(), ctx->csr.vals, v.size() * 8, cudaMemcpyDeviceToHost));
+    uint32_t p = 0;
+    for (uint32_t r = 0; r < ctx->local_rows; r++) {
+        rowptr[r] = p;
+        for (int sl = 0; sl < ctx->slabs; sl++)
+            for (uint32_t q = rp[sl * st + r]; q < rp[sl * st + r + 1]; q++) {
+                colind[p] = ci[q];
+                ((uint64_t *)vals)[p] = v[q];
+                p++;
+            }
+    }
+    rowptr[ctx->local_rows] = p;
+    return 0;
+}
+
+extern "C" int b200spmv_get_csc(b200spmv_ctx *ctx, uint32_t *colptr, uint32_t *rowind, void *vals)
+{
+    B2_NEED_READY(ctx);
+    if (!ctx->csc_colptr) return b2_fail(ctx, B200SPMV_ESTATE, "CSC copy was released (set option keep_csc=1 before setup)");
+    B2_CHECK(ctx, cudaMemcpy(colptr, ctx->csc_colptr, ((size_t)ctx->cols + 1) * 4, cudaMemcpyDeviceToHost));
+    B2_CHECK(ctx, cudaMemcpy(rowind, ctx->csc_rowind, (size_t)ctx->local_nnz * 4, cudaMemcpyDeviceToHost));
+    B2_CHECK(ctx, cudaMemcpy(vals, ctx->csc_vals, (size_t)ctx->local_nnz * 8, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *out)
+{
+    if (!ctx || !key || !out) return B200SPMV_EINVAL;
+    const std::string k(key);
+    if (k == "rows") *out = ctx->rows;
+    else if (k == "cols") *out = ctx->cols;
+    else if (k == "nz") *out = ctx->nnz;
+    else if (k == "local_rows") *out = ctx->local_rows;
+    else if (k == "local_nz") *out = ctx->local_nnz;
+    else if (k == "row_begin") *out = ctx->row_begin;
+    else if (k == "row_end") *out = ctx->row_end;
+    else if (k == "spmvtime_ns") *out = ctx->spmvtime_ns;
+    else if (k == "xfertime_ns") *out = ctx->xfertime_ns;
+    else if (k == "setuptime_ns") *out = ctx->setuptime_ns;
+    else if (k == "transposetime_ns") *out = ctx->transposetime_ns;
+    else if (k == "slabs") *out = (uint64_t)ctx->slabs;
+    else if (k == "l2_persist_bytes") *out = ctx->max_persist_bytes;
+    else if (k == "l2_bytes") *out = ctx->l2_bytes;
+    else if (k == "sms") *out = (uint64_t)ctx->sms;
+    else if (k == "gpus") *out = (uint64_t)ctx->world;
+    else if (k == "rank") *out = (uint64_t)ctx->rank;
+    else if (k == "mode") *out = (uint64_t)ctx->last_mode;
+    else if (k == "launches") *out = ctx->launches;
+    else if (k == "cuda_error") *out = (uint64_t)ctx->cuda_error;
+    else if (k == "tiles") *out = ctx->total_tiles;
+    else if (k == "merge_kernel_ns") { cudaStreamSynchronize(ctx->stream); b2_profile_collect(ctx); *out = ctx->merge_kernel_ns; }
+    else if (k == "merge_kernel_launches") { cudaStreamSynchronize(ctx->stream); b2_profile_collect(ctx); *out = ctx->merge_kernel_launches; }
+    else { *out = 0; return b2_fail(ctx, B200SPMV_EINVAL, "unknown stat key"); }
+    return 0;
+}

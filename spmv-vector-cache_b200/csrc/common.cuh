@@ -1,0 +1,236 @@
+// common.cuh -- context, error plumbing and PTX helpers shared by the kernels.
+#ifndef B200SPMV_COMMON_CUH_
+#define B200SPMV_COMMON_CUH_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+
+#include "../../include/b200spmv.h"
+
+struct ncclComm;
+
+// ---------------------------------------------------------------------------------------
+// Device-resident matrix, one per context.
+//   CSC (as the reference stores it: software/SparseMatrix.h:60-69) is kept only until the
+//   CSR is built unless keep_csc is set (tests / get_csc).
+//   CSR is stored per column slab s: rowptr_s[local_rows+1] (offsets into the rank-local
+//   colind/vals arrays), so that the x slice gathered by one slab pass fits the L2 set-aside.
+// ---------------------------------------------------------------------------------------
+struct DeviceCsr {
+    uint32_t *rowptr = nullptr;  // [slabs][local_rows+1], absolute offsets into colind/vals
+    uint32_t *colind = nullptr;  // [local_nnz (+pad)], GLOBAL column ids
+    void *vals = nullptr;        // [local_nnz (+pad)] 8-byte
+    // merge-path tiling, one table per slab: tile t starts at (row, nz) = tile_row[t], tile_nz[t]
+    uint32_t *tile_row = nullptr;
+    uint32_t *tile_nz = nullptr;
+    uint32_t *tile_base = nullptr;  // [slabs+1] first tile of each slab (host copy in h_tile_base)
+    uint32_t *carry_row = nullptr;  // [tiles] row of the tile's carry-out
+    void *carry_val = nullptr;      // [tiles] 8-byte partial of that row
+};
+
+struct b200spmv_ctx {
+    int device = 0;
+    int sms = 0;
+    size_t l2_bytes = 0;
+    size_t max_persist_bytes = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    int cuda_error = 0;
+
+    // options
+    int opt_slabs = 0;            // 0 = auto
+    int64_t opt_persist_bytes = 0;  // 0 = device max
+    int opt_require_aligned = 0;
+    int opt_keep_csc = 0;
+    int opt_profile = 0;          // 1: bracket every merge-kernel launch with events (bench roofline)
+
+    // matrix
+    bool ready = false;
+    int dtype = B200SPMV_F64;
+    uint32_t rows = 0, cols = 0;
+    uint64_t nnz = 0;             // global
+    uint32_t row_begin = 0, row_end = 0;  // this rank's row block
+    uint32_t local_rows = 0;
+    size_t rowptr_stride = 0;     // elements between the slabs' row-pointer arrays (multiple of 4)
+    uint64_t local_nnz = 0;
+    int slabs = 1;
+    uint32_t slab_cols = 0;       // columns per slab (last may be short)
+    uint32_t h_tile_base[65] = {0};
+    uint32_t total_tiles = 0;
+    DeviceCsr csr;
+    // CSC copy (rank-local entries, global ids)
+    uint32_t *csc_colptr = nullptr, *csc_rowind = nullptr;
+    void *csc_vals = nullptr;
+
+    // vectors (device): x is the full replicated vector, y the full-length result (only
+    // [row_begin,row_end) is written by this rank)
+    void *d_x = nullptr, *d_y = nullptr;
+    void *pin_x = nullptr, *pin_y = nullptr;  // pinned staging for pageable host vectors
+    size_t pin_x_bytes = 0, pin_y_bytes = 0;
+    bool persist_set = false;
+
+    // multi-GPU
+    ncclComm *comm = nullptr;
+    int rank = 0, world = 1;
+    uint32_t *h_row_splits = nullptr;  // [world+1]
+    double *d_norm = nullptr;          // scratch for power iteration
+
+    // stats
+    uint64_t spmvtime_ns = 0, xfertime_ns = 0, setuptime_ns = 0, transposetime_ns = 0;
+    uint64_t launches = 0;
+    cudaEvent_t prof_ev[128] = {nullptr};
+    int prof_n = 0;               // events recorded since the last read
+    uint64_t merge_kernel_ns = 0, merge_kernel_launches = 0;
+    int last_mode = 0;
+};
+
+#define B2_CHECK(ctx, call)                                                              \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess) {                                                          \
+            char buf_[512];                                                               \
+            snprintf(buf_, sizeof buf_, "%s:%d: %s -> %s", __FILE__, __LINE__, #call,     \
+                     cudaGetErrorString(e_));                                             \
+            (ctx)->err = buf_;                                                            \
+            (ctx)->cuda_error = (int)e_;                                                  \
+            return e_ == cudaErrorMemoryAllocation ? B200SPMV_ENOMEM : B200SPMV_ECUDA;    \
+        }                                                                                 \
+    } while (0)
+
+#define B2_TRY(expr)             \
+    do {                         \
+        int rc_ = (expr);        \
+        if (rc_ != 0) return rc_; \
+    } while (0)
+
+static inline int b2_fail(b200spmv_ctx *ctx, int code, const char *msg)
+{
+    if (ctx) ctx->err = msg;
+    return code;
+}
+
+template <typename T>
+static inline int b2_alloc(b200spmv_ctx *ctx, T **p, size_t count)
+{
+    *p = nullptr;
+    // pad every array by 256 bytes so 16-byte-granular tile loads may overrun the logical end
+    B2_CHECK(ctx, cudaMalloc((void **)p, count * sizeof(T) + 256));
+    return 0;
+}
+static inline int b2_alloc_bytes(b200spmv_ctx *ctx, void **p, size_t bytes)
+{
+    *p = nullptr;
+    B2_CHECK(ctx, cudaMalloc(p, bytes + 256));
+    return 0;
+}
+template <typename T>
+static inline void b2_free(T *&p)
+{
+    if (p) cudaFree((void *)p);
+    p = nullptr;
+}
+
+static inline unsigned b2_div_up(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }
+
+// ---- module entry points (host side) ---------------------------------------------------
+// scan.cu
+int b2_exclusive_scan_u32(b200spmv_ctx *ctx, uint32_t *data, uint64_t n, cudaStream_t s);
+size_t b2_scan_scratch_bytes(uint64_t n);
+// sort.cu : stable LSD radix sort of (key, payload) pairs; key_bits significant bits
+int b2_sort_pairs(b200spmv_ctx *ctx, uint32_t *keys, uint32_t *payload, uint32_t *keys_tmp,
+                  uint32_t *payload_tmp, uint64_t n, int key_bits, bool payload_is_iota,
+                  uint32_t **sorted_payload, cudaStream_t s);
+// transpose.cu
+int b2_compress(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *key, uint32_t key_mask,
+                uint32_t key_sub, const uint32_t *src_ptr, uint32_t src_major, uint32_t src_pos_off,
+                const uint32_t *src_other, const void *src_vals, uint32_t *dst_ptr, uint32_t dst_ptr_add,
+                uint32_t *dst_ind, void *dst_vals, cudaStream_t s);
+int b2_add_u32(b200spmv_ctx *ctx, uint32_t *a, uint64_t n, uint32_t add, cudaStream_t s);
+// spmv.cu
+int b2_build_tiles(b200spmv_ctx *ctx);
+int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s);
+void b2_profile_collect(b200spmv_ctx *ctx);
+// synth.cu
+int b2_synth_build_csc(b200spmv_ctx *ctx, int kind, uint32_t npr, uint64_t seed);
+int b2_synth_fill_x(b200spmv_ctx *ctx, uint64_t seed);
+// multi.cu
+int b2_comm_destroy(b200spmv_ctx *ctx);
+int b2_shard_csc(b200spmv_ctx *ctx, uint32_t index_mask);
+
+// ---- device helpers --------------------------------------------------------------------
+#if defined(__CUDACC__)
+
+// L2 eviction policies.  The matrix streams are read once: evict_first, so they do not
+// displace the gathered vector (the "vector cache" contents), which is evict_last.
+// (On sm_100a the direct .L2::evict_* qualifiers exist only for 256-bit loads; narrower
+// loads take a createpolicy descriptor through .L2::cache_hint.)
+__device__ __forceinline__ uint64_t policy_evict_first()
+{
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_last()
+{
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+// streaming 128-bit load: no L1 allocation, L2 policy `pol`
+__device__ __forceinline__ uint4 ld_stream_v4(const void *p, uint64_t pol)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p), "l"(pol));
+    return r;
+}
+// streaming 256-bit load (Blackwell): four 8-byte values, 32-byte aligned
+__device__ __forceinline__ void ld_stream_v4_b64(const void *p, uint64_t (&v)[4])
+{
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
+                 : "l"(p));
+}
+__device__ __forceinline__ uint32_t ld_stream_u32(const void *p, uint64_t pol)
+{
+    uint32_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(r) : "l"(p), "l"(pol));
+    return r;
+}
+// gathered-vector load: read-only path, keep in L2
+__device__ __forceinline__ uint64_t ld_gather_u64(const void *p, uint64_t pol)
+{
+    uint64_t r;
+    asm volatile("ld.global.nc.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(r) : "l"(p), "l"(pol));
+    return r;
+}
+
+// semiring (chisel/frontend/SemiringOp.scala): fp64 = separate IEEE multiply and add, never
+// contracted to FMA; u64 = wrapping.
+template <int DT> struct Semi;
+template <> struct Semi<B200SPMV_F64> {
+    __device__ __forceinline__ static uint64_t mul(uint64_t a, uint64_t b)
+    {
+        return (uint64_t)__double_as_longlong(__dmul_rn(__longlong_as_double((long long)a),
+                                                         __longlong_as_double((long long)b)));
+    }
+    __device__ __forceinline__ static uint64_t add(uint64_t a, uint64_t b)
+    {
+        return (uint64_t)__double_as_longlong(__dadd_rn(__longlong_as_double((long long)a),
+                                                         __longlong_as_double((long long)b)));
+    }
+};
+template <> struct Semi<B200SPMV_U64> {
+    __device__ __forceinline__ static uint64_t mul(uint64_t a, uint64_t b) { return a * b; }
+    __device__ __forceinline__ static uint64_t add(uint64_t a, uint64_t b) { return a + b; }
+};
+#endif  // __CUDACC__
+
+#endif

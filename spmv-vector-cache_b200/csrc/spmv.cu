@@ -1,0 +1,351 @@
+// spmv.cu -- the hot path: y (+)= A*x on the device-resident CSR (software/SoftwareSpMV.cpp:59-64
+// after the CSC->CSR transpose).
+//
+//   spmv_merge_kernel : nnz-balanced merge-path SpMV.  The merge of the row-end offsets with
+//       the nnz indices is cut into tiles of MP_TILE items; a CTA stages one tile's products
+//       val*x[col] in shared memory with 128-bit streaming loads of indices and values, then
+//       every thread walks MP_IPT merge items, rows that straddle threads are completed from
+//       the neighbours' carries, rows that straddle tiles through a carry-out fixed up by
+//       spmv_fixup_kernel.  Re-associates fp64 sums (tolerance mode); u64 is exact.
+//   spmv_rowseq_kernel : one thread per row, entries in CSR (= reference) order, separate
+//       multiply and add: fp64 results memcmp-equal to SoftwareSpMV (strict mode).
+//
+// Column slabs: with S > 1 the CSR is stored slab-major and the kernels run slab by slab, so
+// the x slice gathered at any time fits the L2 set-aside (the "vector cache").
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int MP_THREADS = 256;
+constexpr int MP_IPT = 8;
+constexpr int MP_TILE = MP_THREADS * MP_IPT;  // merge items per tile
+constexpr uint32_t NO_ROW = 0xFFFFFFFFu;
+
+// ---- merge-path partition (once per matrix) --------------------------------------------
+// rowptr: this slab's [rows+1] absolute offsets.  Tile t of the slab starts at merge diagonal
+// t*MP_TILE; writes (rows consumed, absolute nz offset) for t in [0, ntiles].
+__global__ void tile_search_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, uint32_t ntiles,
+                                   uint32_t *__restrict__ tile_row, uint32_t *__restrict__ tile_nz)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > ntiles) return;
+    const uint32_t nz_begin = rowptr[0];
+    const uint64_t nnz = (uint64_t)rowptr[rows] - nz_begin;
+    const uint64_t items = (uint64_t)rows + nnz;
+    const uint64_t diag = min((unsigned long long)t * MP_TILE, (unsigned long long)items);
+    uint64_t lo = diag > nnz ? diag - nnz : 0;
+    uint64_t hi = min((unsigned long long)diag, (unsigned long long)rows);
+    while (lo < hi) {
+        const uint64_t mid = (lo + hi) >> 1;
+        // row-end item `mid` precedes nnz item (diag-mid-1) iff rowend[mid] <= that nnz index
+        if ((uint64_t)(rowptr[mid + 1] - nz_begin) <= diag - mid - 1) lo = mid + 1; else hi = mid;
+    }
+    tile_row[t] = (uint32_t)lo;
+    tile_nz[t] = nz_begin + (uint32_t)(diag - lo);
+}
+
+template <bool PERSIST>
+__device__ __forceinline__ uint64_t load_x(const uint64_t *__restrict__ x, uint32_t col, uint64_t pol)
+{
+    if (PERSIST) return ld_gather_u64(x + col, pol);
+    return __ldg(reinterpret_cast<const unsigned long long *>(x + col));
+}
+
+struct MergeSmem {
+    uint64_t prod[MP_TILE + 4];
+    uint64_t yrow[MP_TILE];
+    uint64_t cval[MP_THREADS];
+    uint32_t rowend[MP_TILE + 1];
+    uint32_t crow[MP_THREADS];
+};
+
+// ---- merge-path SpMV, one tile per CTA ---------------------------------------------------
+// READ_Y: the rows completed here start from the y already in memory (accumulate mode, or any
+// slab after the first); otherwise from the additive identity.
+template <int DT, bool PERSIST, bool READ_Y>
+__global__ void __launch_bounds__(MP_THREADS)
+spmv_merge_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ colind,
+                  const uint64_t *__restrict__ vals, const uint64_t *__restrict__ x,
+                  uint64_t *__restrict__ y, uint32_t rows, const uint32_t *__restrict__ tile_row,
+                  const uint32_t *__restrict__ tile_nz, uint32_t *__restrict__ carry_row,
+                  uint64_t *__restrict__ carry_val)
+{
+    __shared__ __align__(16) MergeSmem sm;
+    const uint32_t t = blockIdx.x;
+    const int tid = threadIdx.x;
+    const uint32_t r0 = tile_row[t], r1 = tile_row[t + 1];
+    const uint32_t nz0 = tile_nz[t], nz1 = tile_nz[t + 1];
+    const uint32_t tile_rows = r1 - r0, tile_nnz = nz1 - nz0;
+    const uint32_t tile_items = tile_rows + tile_nnz;
+
+    // (1) row-end offsets of rows r0..r1 (r1 = the row left open at the end of the tile)
+    for (uint32_t i = tid; i <= tile_rows; i += MP_THREADS) {
+        const uint32_t r = r0 + i;
+        sm.rowend[i] = (r < rows) ? rowptr[r + 1] : 0xFFFFFFFFu;
+    }
+    // (2) stage products: groups of 4 entries from a 16-byte aligned base
+    const uint32_t base = nz0 & ~3u;
+    const uint32_t ngroups = (nz1 - base + 3) >> 2;
+    const uint64_t pol_stream = policy_evict_first(), pol_keep = policy_evict_last();
+    for (uint32_t g = tid; g < ngroups; g += MP_THREADS) {
+        const uint64_t e = (uint64_t)base + 4ull * g;
+        const uint4 c = ld_stream_v4(colind + e, pol_stream);
+        uint64_t vv[4];
+        ld_stream_v4_b64(vals + e, vv);
+        const uint32_t cc[4] = {c.x, c.y, c.z, c.w};
+        uint64_t xv[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) xv[k] = (e + k < nz1) ? load_x<PERSIST>(x, cc[k], pol_keep) : 0ull;
+#pragma unroll
+        for (int k = 0; k < 4; k++) sm.prod[4 * g + k] = Semi<DT>::mul(vv[k], xv[k]);
+    }
+    __syncthreads();
+
+    // (3) each thread walks MP_IPT merge items starting at its diagonal
+    const uint32_t diag = min((uint32_t)tid * MP_IPT, tile_items);
+    uint32_t lo = diag > tile_nnz ? diag - tile_nnz : 0u;
+    uint32_t hi = min(diag, tile_rows);
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (sm.rowend[mid] <= nz0 + (diag - mid - 1)) lo = mid + 1; else hi = mid;
+    }
+    uint32_t r = lo;                    // local row
+    uint32_t nz = nz0 + (diag - lo);    // absolute nz
+    const uint32_t first_row = r;
+    bool emitted = false;
+    uint64_t acc = 0;
+    uint32_t row_end = sm.rowend[r];
+#pragma unroll
+    for (int k = 0; k < MP_IPT; k++) {
+        if (diag + k < tile_items) {
+            if (nz < row_end) {
+                acc = Semi<DT>::add(acc, sm.prod[nz - base]);
+                nz++;
+            } else {
+                sm.yrow[r] = acc;
+                emitted = true;
+                acc = 0;
+                r++;
+                row_end = sm.rowend[r];
+            }
+        }
+    }
+    sm.crow[tid] = r;
+    sm.cval[tid] = acc;
+    __syncthreads();
+
+    // (4) the first row a thread completed may have begun in earlier threads: add their carries
+    if (emitted) {
+        int k = tid;
+        while (k > 0 && sm.crow[k - 1] == first_row) k--;
+        if (k < tid) {
+            uint64_t c = sm.cval[k];
+            for (int q = k + 1; q < tid; q++) c = Semi<DT>::add(c, sm.cval[q]);
+            sm.yrow[first_row] = Semi<DT>::add(c, sm.yrow[first_row]);
+        }
+    }
+    // tile carry-out: the partial of the row left open (threads whose walk ended in it)
+    if (tid == MP_THREADS - 1) {
+        const bool has_items = tile_rows > 0 ? (nz1 > sm.rowend[tile_rows - 1]) : (tile_nnz > 0);
+        int k = tid;
+        while (k > 0 && sm.crow[k - 1] == tile_rows) k--;
+        uint64_t c = sm.cval[k];
+        for (int q = k + 1; q <= tid; q++) c = Semi<DT>::add(c, sm.cval[q]);
+        carry_row[t] = has_items ? r1 : NO_ROW;
+        carry_val[t] = c;
+    }
+    __syncthreads();
+
+    // (5) coalesced write of the rows completed in this tile
+    for (uint32_t i = tid; i < tile_rows; i += MP_THREADS) {
+        uint64_t v = sm.yrow[i];
+        if (READ_Y) v = Semi<DT>::add(y[r0 + i], v);
+        y[r0 + i] = v;
+    }
+}
+
+// Carries of rows that straddle tiles: the head of each run of equal carry rows adds the run
+// (in tile order) to y.  Runs after spmv_merge_kernel on the same stream.
+template <int DT>
+__global__ void spmv_fixup_kernel(const uint32_t *__restrict__ carry_row, const uint64_t *__restrict__ carry_val,
+                                  uint32_t ntiles, uint64_t *__restrict__ y)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntiles) return;
+    const uint32_t row = carry_row[t];
+    if (row == NO_ROW) return;
+    if (t > 0 && carry_row[t - 1] == row) return;  // not the head of its run
+    uint64_t c = carry_val[t];
+    for (uint32_t q = t + 1; q < ntiles && carry_row[q] == row; q++) c = Semi<DT>::add(c, carry_val[q]);
+    y[row] = Semi<DT>::add(c, y[row]);
+}
+
+// ---- strict order: one thread per row, reference summation order -------------------------
+template <int DT, bool READ_Y>
+__global__ void __launch_bounds__(256)
+spmv_rowseq_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ colind,
+                   const uint64_t *__restrict__ vals, const uint64_t *__restrict__ x,
+                   uint64_t *__restrict__ y, uint32_t rows)
+{
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= rows) return;
+    uint64_t acc = READ_Y ? y[r] : 0ull;
+    const uint32_t end = rowptr[r + 1];
+    for (uint32_t p = rowptr[r]; p < end; p++)
+        acc = Semi<DT>::add(acc, Semi<DT>::mul(vals[p], x[colind[p]]));  // mul then add, never FMA
+    y[r] = acc;
+}
+
+}  // namespace
+
+// ---- host side -----------------------------------------------------------------------------
+
+// Merge-path tile tables for every slab.  Slab s owns tile-table entries
+// [h_tile_base[s] + s, h_tile_base[s+1] + s] (ntiles_s + 1 of them) and carries [h_tile_base[s], ..).
+int b2_build_tiles(b200spmv_ctx *ctx)
+{
+    DeviceCsr &m = ctx->csr;
+    b2_free(m.tile_row); b2_free(m.tile_nz); b2_free(m.carry_row);
+    { uint64_t *cv = (uint64_t *)m.carry_val; b2_free(cv); m.carry_val = nullptr; }
+    std::vector<uint32_t> h_ptr(2 * (size_t)ctx->slabs);
+    const size_t stride = ctx->rowptr_stride;
+    uint32_t total = 0;
+    for (int s = 0; s < ctx->slabs; s++) {
+        uint32_t b = 0, e = 0;
+        B2_CHECK(ctx, cudaMemcpy(&b, m.rowptr + s * stride, 4, cudaMemcpyDeviceToHost));
+        B2_CHECK(ctx, cudaMemcpy(&e, m.rowptr + s * stride + ctx->local_rows, 4, cudaMemcpyDeviceToHost));
+        const uint64_t items = (uint64_t)ctx->local_rows + (e - b);
+        ctx->h_tile_base[s] = total;
+        total += b2_div_up(items, MP_TILE);
+    }
+    ctx->h_tile_base[ctx->slabs] = total;
+    ctx->total_tiles = total;
+    B2_TRY(b2_alloc(ctx, &m.tile_row, (size_t)total + ctx->slabs));
+    B2_TRY(b2_alloc(ctx, &m.tile_nz, (size_t)total + ctx->slabs));
+    B2_TRY(b2_alloc(ctx, &m.carry_row, (size_t)total + 1));
+    uint64_t *cv = nullptr;
+    B2_TRY(b2_alloc(ctx, &cv, (size_t)total + 1));
+    m.carry_val = cv;
+    for (int s = 0; s < ctx->slabs; s++) {
+        const uint32_t nt = ctx->h_tile_base[s + 1] - ctx->h_tile_base[s];
+        tile_search_kernel<<<b2_div_up((uint64_t)nt + 1, 256), 256, 0, ctx->stream>>>(
+            m.rowptr + s * stride, ctx->local_rows, nt, m.tile_row + ctx->h_tile_base[s] + s,
+            m.tile_nz + ctx->h_tile_base[s] + s);
+        B2_CHECK(ctx, cudaGetLastError());
+    }
+    B2_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+static int set_persist_window(b200spmv_ctx *ctx, cudaStream_t s, const void *base, size_t bytes, bool on)
+{
+    cudaStreamAttrValue attr;
+    memset(&attr, 0, sizeof attr);
+    if (on && ctx->max_persist_bytes > 0 && bytes > 0) {
+        int max_win = 0;
+        cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, ctx->device);
+        const size_t win = std::min(bytes, (size_t)max_win);
+        size_t set_aside = ctx->max_persist_bytes;
+        if (ctx->opt_persist_bytes > 0) set_aside = std::min(set_aside, (size_t)ctx->opt_persist_bytes);
+        attr.accessPolicyWindow.base_ptr = const_cast<void *>(base);
+        attr.accessPolicyWindow.num_bytes = win;
+        attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)set_aside / (double)win);
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    } else {
+        attr.accessPolicyWindow.num_bytes = 0;
+        attr.accessPolicyWindow.hitRatio = 0.f;
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+    }
+    B2_CHECK(ctx, cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr));
+    return 0;
+}
+
+template <int DT>
+static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
+{
+    const DeviceCsr &m = ctx->csr;
+    const bool strict = flags & B200SPMV_STRICT_ORDER;
+    const bool persist = !(flags & B200SPMV_NO_PERSIST);
+    const bool accumulate = flags & B200SPMV_ACCUMULATE;
+    const uint64_t *x = (const uint64_t *)ctx->d_x;
+    uint64_t *y = (uint64_t *)ctx->d_y + ctx->row_begin;
+    const uint64_t *vals = (const uint64_t *)m.vals;
+    const size_t stride = ctx->rowptr_stride;
+    const uint32_t rows = ctx->local_rows;
+    if (rows == 0) return 0;
+    for (int sl = 0; sl < ctx->slabs; sl++) {
+        const uint32_t *rowptr = m.rowptr + sl * stride;
+        const bool read_y = accumulate || sl > 0;
+        if (persist != ctx->persist_set || ctx->slabs > 1) {
+            const size_t c0 = (size_t)sl * ctx->slab_cols;
+            const size_t c1 = std::min<size_t>(ctx->cols, c0 + ctx->slab_cols);
+            B2_TRY(set_persist_window(ctx, s, x + c0, (c1 - c0) * 8, persist));
+            ctx->persist_set = persist;
+        }
+        if (strict) {
+            const unsigned grid = b2_div_up(rows, 256);
+            if (read_y) spmv_rowseq_kernel<DT, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows);
+            else spmv_rowseq_kernel<DT, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows);
+            ctx->launches += 1;
+        } else {
+            const uint32_t tb = ctx->h_tile_base[sl];
+            const uint32_t nt = ctx->h_tile_base[sl + 1] - tb;
+            if (nt == 0) continue;
+            const uint32_t *trow = m.tile_row + tb + sl, *tnz = m.tile_nz + tb + sl;
+            uint32_t *crow = m.carry_row + tb;
+            uint64_t *cval = (uint64_t *)m.carry_val + tb;
+#define B2_LAUNCH_MERGE(P, R) \
+    spmv_merge_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval)
+            const bool prof = ctx->opt_profile && ctx->prof_n + 2 <= 128;
+            if (prof) {
+                if (!ctx->prof_ev[ctx->prof_n]) { cudaEventCreate(&ctx->prof_ev[ctx->prof_n]); cudaEventCreate(&ctx->prof_ev[ctx->prof_n + 1]); }
+                cudaEventRecord(ctx->prof_ev[ctx->prof_n], s);
+            }
+            if (persist) { if (read_y) B2_LAUNCH_MERGE(true, true); else B2_LAUNCH_MERGE(true, false); }
+            else { if (read_y) B2_LAUNCH_MERGE(false, true); else B2_LAUNCH_MERGE(false, false); }
+#undef B2_LAUNCH_MERGE
+            if (prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
+            spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
+            ctx->launches += 2;
+        }
+        B2_CHECK(ctx, cudaGetLastError());
+    }
+    ctx->last_mode = strict ? 0 : 1;
+    return 0;
+}
+
+// Fold the recorded merge-kernel event pairs into merge_kernel_ns (call after a sync).
+void b2_profile_collect(b200spmv_ctx *ctx)
+{
+    for (int i = 0; i + 1 < ctx->prof_n; i += 2) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ctx->prof_ev[i], ctx->prof_ev[i + 1]) == cudaSuccess) {
+            ctx->merge_kernel_ns += (uint64_t)((double)ms * 1e6);
+            ctx->merge_kernel_launches++;
+        }
+    }
+    ctx->prof_n = 0;
+}
+
+int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s)
+{
+    static bool carveout_set = false;
+    if (!carveout_set) {
+#define B2_CARVE(DT) \
+    cudaFuncSetAttribute(spmv_merge_kernel<DT, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
+    cudaFuncSetAttribute(spmv_merge_kernel<DT, true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
+    cudaFuncSetAttribute(spmv_merge_kernel<DT, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
+    cudaFuncSetAttribute(spmv_merge_kernel<DT, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        B2_CARVE(B200SPMV_F64)
+        B2_CARVE(B200SPMV_U64)
+#undef B2_CARVE
+        carveout_set = true;
+    }
+    return ctx->dtype == B200SPMV_F64 ? launch_dtype<B200SPMV_F64>(ctx, flags, s)
+                                      : launch_dtype<B200SPMV_U64>(ctx, flags, s);
+}

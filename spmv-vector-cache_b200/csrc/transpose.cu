@@ -1,0 +1,99 @@
+// transpose.cu -- compressed-format transpose on the device (CSC -> CSR and back).
+//
+// Device analogue of software/csr2csc.c:11-39 with the roles of rows and columns
+// selectable: count per destination segment (:20) -> running sum (:22) -> STABLE scatter
+// (:27-33).  The stable scatter is done as a stable radix sort of (destination id, source
+// position) pairs (sort.cu) followed by one gather, because a parallel cursor scatter
+// cannot keep storage order inside a segment.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace {
+
+__global__ void keys_count_kernel(const uint32_t *__restrict__ key, uint32_t mask, uint32_t sub, uint64_t n,
+                                  uint32_t *__restrict__ keys_out, uint32_t *__restrict__ counts)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += stride) {
+        const uint32_t k = (key[e] & mask) - sub;
+        keys_out[e] = k;
+        atomicAdd(&counts[k], 1u);  // csr2csc.c:20
+    }
+}
+
+// segment that owns source position e: last s with ptr[s] <= e (empty segments skipped)
+__device__ __forceinline__ uint32_t owner_segment(const uint32_t *__restrict__ ptr, uint32_t nseg, uint32_t e)
+{
+    uint32_t lo = 0, hi = nseg;  // invariant: ptr[lo] <= e < ptr[hi]
+    while (hi - lo > 1) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        if (__ldg(ptr + mid) <= e) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void gather_kernel(const uint32_t *__restrict__ perm, uint64_t n,
+                              const uint32_t *__restrict__ src_ptr, uint32_t src_major, uint32_t src_pos_off,
+                              const uint32_t *__restrict__ src_other, const uint64_t *__restrict__ src_vals,
+                              uint32_t *__restrict__ dst_ind, uint64_t *__restrict__ dst_vals)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
+        const uint32_t e = perm[p];
+        dst_ind[p] = src_other ? src_other[e] : owner_segment(src_ptr, src_major, e + src_pos_off);
+        if (src_vals) dst_vals[p] = src_vals[e];
+    }
+}
+
+__global__ void add_u32_kernel(uint32_t *__restrict__ a, uint64_t n, uint32_t add)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) a[i] += add;
+}
+
+}  // namespace
+
+int b2_add_u32(b200spmv_ctx *ctx, uint32_t *a, uint64_t n, uint32_t add, cudaStream_t s)
+{
+    if (n == 0 || add == 0) return 0;
+    add_u32_kernel<<<(unsigned)std::min<uint64_t>(b2_div_up(n, 256), (uint64_t)ctx->sms * 32), 256, 0, s>>>(a, n, add);
+    B2_CHECK(ctx, cudaGetLastError());
+    return 0;
+}
+
+// Group n entries by key into nkeys segments, stable.
+//   (key[e] & key_mask) - key_sub : destination segment of entry e (row id for CSC->CSR)
+//   the entry's other index: src_other[e] (COO input) or, when src_other == nullptr, the
+//   segment of the compressed source that holds position e + src_pos_off (src_ptr[src_major+1])
+// Outputs dst_ptr[nkeys+1] (+ dst_ptr_add on every element), dst_ind[n], dst_vals[n] (8-byte, optional).
+int b2_compress(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *key, uint32_t key_mask,
+                uint32_t key_sub, const uint32_t *src_ptr, uint32_t src_major, uint32_t src_pos_off,
+                const uint32_t *src_other, const void *src_vals, uint32_t *dst_ptr, uint32_t dst_ptr_add,
+                uint32_t *dst_ind, void *dst_vals, cudaStream_t s)
+{
+    B2_CHECK(ctx, cudaMemsetAsync(dst_ptr, 0, ((size_t)nkeys + 1) * sizeof(uint32_t), s));
+    if (n == 0) return b2_add_u32(ctx, dst_ptr, (uint64_t)nkeys + 1, dst_ptr_add, s);
+    uint32_t *k0 = nullptr, *k1 = nullptr, *p0 = nullptr, *p1 = nullptr, *perm = nullptr;
+    int rc = 0;
+    do {
+        if ((rc = b2_alloc(ctx, &k0, n))) break;
+        if ((rc = b2_alloc(ctx, &k1, n))) break;
+        if ((rc = b2_alloc(ctx, &p0, n))) break;
+        if ((rc = b2_alloc(ctx, &p1, n))) break;
+        const unsigned grid = (unsigned)std::min<uint64_t>(b2_div_up(n, 256), (uint64_t)ctx->sms * 32);
+        keys_count_kernel<<<grid, 256, 0, s>>>(key, key_mask, key_sub, n, k0, dst_ptr);
+        if ((rc = b2_exclusive_scan_u32(ctx, dst_ptr, (uint64_t)nkeys + 1, s))) break;  // csr2csc.c:22
+        if ((rc = b2_add_u32(ctx, dst_ptr, (uint64_t)nkeys + 1, dst_ptr_add, s))) break;
+        int key_bits = 1;
+        while (key_bits < 32 && (1ull << key_bits) < (uint64_t)nkeys) key_bits++;
+        if ((rc = b2_sort_pairs(ctx, k0, p0, k1, p1, n, key_bits, true, &perm, s))) break;
+        gather_kernel<<<grid, 256, 0, s>>>(perm, n, src_ptr, src_major, src_pos_off, src_other,
+                                           (const uint64_t *)src_vals, dst_ind, (uint64_t *)dst_vals);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; rc = B200SPMV_ECUDA; }
+    } while (0);
+    b2_free(k0); b2_free(k1); b2_free(p0); b2_free(p1);
+    return rc;
+}

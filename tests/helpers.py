@@ -103,6 +103,7 @@ class OracleLib:
         L.oracle_time_spmv_csc_f64.restype = C.c_double
         L.oracle_power_iterate_f64.restype = C.c_double
         L.synth_host_nnz.restype = C.c_uint64
+        L.synth_host_row_dot.restype = C.c_uint64
 
     def spmv_csc(self, dtype, rows, cols, colptr, rowind, vals, x, y, mask=0xFFFFFFFF):
         fn = self.lib.oracle_spmv_csc_f64 if dtype == "f64" else self.lib.oracle_spmv_csc_u64
@@ -159,6 +160,13 @@ class OracleLib:
         x = np.zeros(n, dtype=np.uint64)
         self.lib.synth_host_x(C.c_uint64(seed), C.c_uint64(n), C.c_int(1 if dtype == "u64" else 0), ptr(x))
         return x.view(np.float64 if dtype == "f64" else np.uint64)
+
+    def synth_row_dot(self, kind, seed, r, rows, cols, npr, dtype, xseed):
+        mag = C.c_double(0.0)
+        bits = self.lib.synth_host_row_dot(C.c_int(kind), C.c_uint64(seed), C.c_uint32(r), C.c_uint32(rows),
+                                           C.c_uint32(cols), C.c_uint32(npr), C.c_int(1 if dtype == "u64" else 0),
+                                           C.c_uint64(xseed), C.byref(mag))
+        return int(bits), mag.value
 
     def synth_csc(self, kind, seed, rows, cols, npr, dtype, scale=None):
         """Host CSC (the reference's layout) of a synthetic matrix, via CSR/COO -> counting sort."""

@@ -1,0 +1,137 @@
+"""GPU tests on the synthetic matrices of BASELINE.json's configs: small sizes against the
+oracle on the host mirror of the generator; full size through size-independent properties."""
+import numpy as np
+import pytest
+
+import helpers as H
+
+pytestmark = pytest.mark.gpu
+SEED = 0x5EED5EED
+EPS = 2.0 ** -53
+
+
+@pytest.fixture(scope="module")
+def b2():
+    import b200spmv
+    return b200spmv
+
+
+def DT(b2, dtype):
+    return b2.F64 if dtype == "f64" else b2.U64
+
+
+@pytest.mark.parametrize("kind,rows,npr", [(0, 5000, 32), (0, 777, 1), (2, 4099, 5), (1, 4096, 8), (1, 1 << 14, 32)])
+@pytest.mark.parametrize("dtype", ["f64", "u64"])
+@pytest.mark.parametrize("slabs", [1, 3])
+def test_synthetic_small_vs_oracle(b2, oracle, kind, rows, npr, dtype, slabs):
+    e = b2.Engine(0)
+    e.set_option("keep_csc", 1)
+    e.set_option("slabs", slabs)
+    e.setup_synthetic(kind, rows, rows, npr, SEED, DT(b2, dtype))
+    # (1) the device generator + CSR->CSC transpose equal the host mirror, bit for bit
+    cp, ri, v = e.get_csc()
+    scale = int(np.log2(rows)) if kind == 1 else None
+    cp_h, ri_h, v_h = oracle.synth_csc(kind, SEED, rows, rows, npr, dtype, scale=scale)
+    assert (cp == cp_h).all() and (ri == ri_h).all() and v.tobytes() == v_h.tobytes()
+    # (2) the CSR used by the kernels is the stable transpose of that CSC
+    rp, ci, vv = e.get_csr()
+    rp_o, ci_o, v_o = oracle.transpose(rows, rows, cp, ri, v)
+    assert (rp == rp_o).all() and (ci == ci_o).all() and vv.tobytes() == v_o.tobytes()
+    # (3) SpMV on the device-resident synthetic x against the reference loop
+    e.fill_x_synthetic(SEED + 1)
+    x = e.get_x()
+    assert x.tobytes() == oracle.synth_x(SEED + 1, rows, dtype).tobytes()
+    want = oracle.spmv_csc(dtype, rows, rows, cp, ri, v, x, np.zeros(rows, dtype=v.dtype))
+    e.exec_device(1, b2.STRICT_ORDER)
+    assert e.get_y().tobytes() == want.tobytes()
+    e.exec_device(2, 0)  # y = A*x twice: idempotent without ACCUMULATE
+    y = e.get_y()
+    if dtype == "u64":
+        assert y.tobytes() == want.tobytes()
+    else:
+        abs_sum = np.zeros(rows)
+        row_nnz = np.zeros(rows, dtype=np.uint32)
+        oracle.lib.oracle_row_abs_sums_f64(H.C.c_uint32(rows), H.C.c_uint32(rows), H.ptr(cp), H.ptr(ri), H.ptr(v),
+                                           H.ptr(x), H.ptr(abs_sum), H.ptr(row_nnz))
+        assert (np.abs(y - want) <= 2.0 * row_nnz * EPS * abs_sum).all()
+    # (4) accumulate on the device: y <- y + A*x
+    e.exec_device(1, b2.ACCUMULATE | b2.STRICT_ORDER)
+    want2 = oracle.spmv_csc(dtype, rows, rows, cp, ri, v, x, y.copy())
+    assert e.get_y().tobytes() == want2.tobytes()
+    e.close()
+
+
+@pytest.mark.parametrize("dtype", ["u64", "f64"])
+def test_headline_config_full_size_properties(b2, oracle, dtype):
+    """configs[2]: uniform 16M x 16M, 32 nnz/row.  Too large for the host oracle, so:
+    rows regenerated on the host from the counter-based definition (spot check, exact for
+    u64 / strict fp64), merge-path == strict kernel (u64 bit-exact), and linearity."""
+    rows, npr = 1 << 24, 32
+    e = b2.Engine(0)
+    e.setup_synthetic(0, rows, rows, npr, SEED, DT(b2, dtype))
+    assert e.stat("nz") == rows * npr
+    e.fill_x_synthetic(SEED + 1)
+    e.exec_device(1, b2.STRICT_ORDER)
+    y_strict = e.get_y()
+    rng = np.random.default_rng(7)
+    picks = np.concatenate([[0, 1, rows - 1], rng.integers(0, rows, 2000)])
+    for r in picks:
+        bits, mag = oracle.synth_row_dot(0, SEED, int(r), rows, rows, npr, dtype, SEED + 1)
+        assert int(y_strict.view(np.uint64)[r]) == bits
+    e.exec_device(1, 0)
+    y_merge = e.get_y()
+    if dtype == "u64":
+        assert y_merge.tobytes() == y_strict.tobytes()
+        # linearity mod 2^64: A*(2x) = 2*(A*x); accumulate: y + A*x = 2*A*x
+        e.exec_device(1, b2.ACCUMULATE)
+        assert e.get_y().tobytes() == (y_strict * np.uint64(2)).tobytes()
+    else:
+        for r in picks:
+            bits, mag = oracle.synth_row_dot(0, SEED, int(r), rows, rows, npr, dtype, SEED + 1)
+            ref = np.array([bits], dtype=np.uint64).view(np.float64)[0]
+            assert abs(y_merge[r] - ref) <= 2 * npr * EPS * mag
+        assert np.allclose(y_merge, y_strict, rtol=0, atol=2 * npr * EPS * 32)
+    e.close()
+
+
+@pytest.mark.parametrize("name", ["circuit204", "row64k", "i1k", "dia64-uint64", "rowvec64-uint64"])
+def test_row_marking_on_device(b2, oracle, name):
+    import os
+    m = H.load_matrix_dir(os.path.join(H.MATRICES, name))
+    e = b2.Engine(0)
+    for reverse, shift in ((0, 31), (1, 30)):
+        a, b = m.rowind.copy(), m.rowind.copy()
+        oracle.lib.oracle_mark_row_starts(H.C.c_uint32(m.rows), H.C.c_uint32(m.nnz), H.ptr(a), reverse, shift)
+        e.mark_row_starts(m.rows, b, reverse, shift)
+        assert (a == b).all()
+    a, b = m.rowind.copy(), m.rowind.copy()
+    want = oracle.lib.oracle_max_alive(H.C.c_uint32(m.rows), H.C.c_uint32(m.nnz), H.ptr(a))
+    assert e.max_alive(m.rows, b) == want and (a == b).all()
+    want = oracle.lib.oracle_max_col_span(H.C.c_uint32(m.cols), H.C.c_uint32(m.nnz), H.ptr(m.colptr), H.ptr(m.rowind))
+    assert e.max_col_span(m.cols, m.colptr, m.rowind) == want
+    e.close()
+
+
+@pytest.mark.parametrize("dtype", ["f64", "u64"])
+def test_power_iteration_single_gpu(b2, oracle, dtype):
+    n, npr, steps = 20000, 5, 6
+    e = b2.Engine(0)
+    e.set_option("keep_csc", 1)
+    e.setup_synthetic(2, n, n, npr, SEED, DT(b2, dtype))
+    cp, ri, v = e.get_csc()
+    ms, nrm = e.power_iterate(steps, False, b2.STRICT_ORDER)
+    x_gpu = e.get_x()
+    if dtype == "u64":
+        x = np.ones(n, dtype=np.uint64)
+        y = np.zeros(n, dtype=np.uint64)
+        oracle.lib.oracle_power_iterate_u64(H.C.c_uint32(n), H.ptr(cp), H.ptr(ri), H.ptr(v), H.ptr(x), H.ptr(y), steps)
+        assert x_gpu.tobytes() == x.tobytes()
+    else:
+        x = np.full(n, 1.0 / np.sqrt(n))
+        y = np.zeros(n)
+        want = oracle.lib.oracle_power_iterate_f64(H.C.c_uint32(n), H.ptr(cp), H.ptr(ri), H.ptr(v), H.ptr(x), H.ptr(y), steps)
+        # the norm is summed in a different order on the device: tolerance, not bits
+        assert abs(nrm - want) <= 1e-12 * want
+        assert np.allclose(x_gpu, x, rtol=1e-11, atol=1e-15)
+    assert ms > 0
+    e.close()

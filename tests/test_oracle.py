@@ -144,7 +144,7 @@ def test_row_marking_vs_reference(oracle, reflib, name):
     mb = reflib.f64.ref_f64_max_alive(H.C.c_uint(m.rows), H.C.c_uint(m.nnz), H.ptr(b))
     assert ma == mb and (a == b).all()
     if name != "dia64-uint64":  # empty column 0: the reference reads inds[-1] there
-        sa = oracle.lib.oracle_max_col_span(H.C.c_uint32(m.cols), H.ptr(m.colptr), H.ptr(m.rowind))
+        sa = oracle.lib.oracle_max_col_span(H.C.c_uint32(m.cols), H.C.c_uint32(m.nnz), H.ptr(m.colptr), H.ptr(m.rowind))
         sb = reflib.f64.ref_f64_max_col_span(H.C.c_uint(m.cols), H.C.c_uint(m.nnz), H.ptr(m.colptr), H.ptr(m.rowind))
         assert sa == sb
 
