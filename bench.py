@@ -181,6 +181,8 @@ def run_ours(args):
         eng.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
     if args.slabs:
         eng.set_option("slabs", args.slabs)
+    if args.kernel:
+        eng.set_option("kernel", args.kernel)
     t0 = time.perf_counter()
     eng.setup_synthetic(kind, rows, cols, npr, SEED, b2.F64)
     setup_s = time.perf_counter() - t0
@@ -288,6 +290,7 @@ def main():
     ap.add_argument("--workload", default="uniform", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the row count (experiments only)")
     ap.add_argument("--slabs", type=int, default=0)
+    ap.add_argument("--kernel", type=int, default=0, help="merge kernel: 1 LDG-staged, 2 TMA-staged (default)")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
     ap.add_argument("--no-persist", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -48,6 +48,7 @@ struct b200spmv_ctx {
     int64_t opt_persist_bytes = 0;  // 0 = device max
     int opt_require_aligned = 0;
     int opt_keep_csc = 0;
+    int opt_kernel = 2;           // merge-path kernel: 1 = LDG-staged (v1), 2 = TMA-staged (v2)
     int opt_profile = 0;          // 1: bracket every merge-kernel launch with events (bench roofline)
 
     // matrix

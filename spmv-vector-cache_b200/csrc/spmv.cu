@@ -167,6 +167,157 @@ spmv_merge_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restric
     }
 }
 
+// ---- merge-path SpMV v2: TMA-staged tile, register accumulation ----------------------------
+// One CTA per tile, like v1, but (a) the tile's column indices, values and row-end offsets are
+// brought into shared memory by three 1-D bulk async copies (TMA, cp.async.bulk) issued by one
+// thread and signalled on an mbarrier -- no LSU wavefronts and no registers are spent on the
+// streams, and with 6 CTAs resident per SM ~200 KB of stream data is in flight per SM;
+// (b) every thread resolves its MP_IPT merge items first (which are entries, which are row
+// ends), issues all its x gathers back to back, then accumulates in registers: products never
+// go through shared memory; (c) completed rows are stored straight to y.
+// The LSU is left to what bounds this kernel on a matrix without locality: one L2 sector
+// request per gathered x element (profiles/r01_gather_ceiling.txt).
+struct TmaSmem {
+    uint64_t val[MP_TILE + 8];
+    uint64_t cval[MP_THREADS];
+    uint32_t col[MP_TILE + 8];
+    uint32_t rowend[MP_TILE + 12];
+    uint32_t crow[MP_THREADS];
+    uint64_t mbar;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void tma_load_1d(void *dst_smem, const void *src, uint32_t bytes, uint64_t *mbar, uint64_t pol)
+{
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+        ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(mbar)), "l"(pol) : "memory");
+}
+
+template <int DT, bool PERSIST, bool READ_Y>
+__global__ void __launch_bounds__(MP_THREADS, 6)
+spmv_merge_tma_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ colind,
+                      const uint64_t *__restrict__ vals, const uint64_t *__restrict__ x,
+                      uint64_t *__restrict__ y, uint32_t rows, const uint32_t *__restrict__ tile_row,
+                      const uint32_t *__restrict__ tile_nz, uint32_t *__restrict__ carry_row,
+                      uint64_t *__restrict__ carry_val)
+{
+    __shared__ __align__(128) TmaSmem sm;
+    const uint32_t t = blockIdx.x;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&sm.mbar)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    const uint32_t r0 = __ldg(tile_row + t), r1 = __ldg(tile_row + t + 1);
+    const uint32_t nz0 = __ldg(tile_nz + t), nz1 = __ldg(tile_nz + t + 1);
+    const uint32_t tile_rows = r1 - r0, tile_nnz = nz1 - nz0;
+    const uint32_t tile_items = tile_rows + tile_nnz;
+    const uint32_t base = nz0 & ~3u;                       // 16-byte aligned start of the entry streams
+    const uint32_t cnt = (nz1 - base + 3u) & ~3u;          // entries copied (multiple of 4)
+    const uint32_t rbase = (r0 + 1u) & ~3u;                // rowptr[r0+1 .. r1+1] = row ends of rows r0..r1
+    const uint32_t rcnt = (r1 + 2u - rbase + 3u) & ~3u;
+    const uint32_t roff = r0 + 1u - rbase;
+    __syncthreads();
+    if (tid == 0) {
+        const uint64_t pol = policy_evict_first();
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&sm.mbar)),
+                     "r"(cnt * 12u + rcnt * 4u) : "memory");
+        tma_load_1d(sm.rowend, rowptr + rbase, rcnt * 4u, &sm.mbar, pol);
+        if (cnt) {
+            tma_load_1d(sm.col, colind + base, cnt * 4u, &sm.mbar, pol);
+            tma_load_1d(sm.val, vals + base, cnt * 8u, &sm.mbar, pol);
+        }
+    }
+    {   // wait for the three copies (phase 0)
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(smem_u32(&sm.mbar)) : "memory");
+    }
+    const uint32_t *rowend = sm.rowend + roff;             // rowend[i] = end offset of local row i
+
+    // merge-path start of this thread inside the tile
+    const uint32_t diag = min((uint32_t)tid * MP_IPT, tile_items);
+    uint32_t lo = diag > tile_nnz ? diag - tile_nnz : 0u;
+    uint32_t hi = min(diag, tile_rows);
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (rowend[mid] <= nz0 + (diag - mid - 1)) lo = mid + 1; else hi = mid;
+    }
+    const uint32_t first_row = lo;
+    const uint32_t nz_first = nz0 + (diag - lo);
+    // pass 1: which of my items are row ends (bit k), how many are entries
+    uint32_t r = lo, nz = nz_first, ends = 0;
+    uint32_t row_end = rowend[r];
+#pragma unroll
+    for (int k = 0; k < MP_IPT; k++) {
+        if (diag + k < tile_items) {
+            if (nz < row_end) nz++;
+            else { ends |= 1u << k; r++; row_end = rowend[r]; }
+        }
+    }
+    // pass 2: all gathers in flight together.  Item k, when it is an entry, is my
+    // (k - #row-ends before k)-th entry.
+    const uint64_t pol_keep = policy_evict_last();
+    const uint32_t off = nz_first - base;
+    uint64_t xv[MP_IPT];
+#pragma unroll
+    for (int k = 0; k < MP_IPT; k++) {
+        const bool is_entry = (diag + k < tile_items) && !((ends >> k) & 1u);
+        const uint32_t jk = k - __popc(ends & ((1u << k) - 1u));
+        xv[k] = is_entry ? load_x<PERSIST>(x, sm.col[off + jk], pol_keep) : 0ull;
+    }
+    // pass 3: accumulate in merge order
+    uint64_t acc = 0, first_val = 0;
+    bool emitted = false;
+    uint32_t rr = first_row;
+#pragma unroll
+    for (int k = 0; k < MP_IPT; k++) {
+        if (diag + k < tile_items) {
+            if ((ends >> k) & 1u) {
+                if (!emitted) { first_val = acc; emitted = true; }
+                else {
+                    uint64_t v = acc;
+                    if (READ_Y) v = Semi<DT>::add(y[r0 + rr], v);
+                    y[r0 + rr] = v;
+                }
+                acc = 0;
+                rr++;
+            } else {
+                const uint32_t jk = k - __popc(ends & ((1u << k) - 1u));
+                acc = Semi<DT>::add(acc, Semi<DT>::mul(sm.val[off + jk], xv[k]));
+            }
+        }
+    }
+    sm.crow[tid] = rr;
+    sm.cval[tid] = acc;
+    __syncthreads();
+
+    if (emitted) {  // my first completed row may have begun in earlier threads
+        int k = tid;
+        while (k > 0 && sm.crow[k - 1] == first_row) k--;
+        uint64_t v = first_val;
+        if (k < tid) {
+            uint64_t c = sm.cval[k];
+            for (int q = k + 1; q < tid; q++) c = Semi<DT>::add(c, sm.cval[q]);
+            v = Semi<DT>::add(c, v);
+        }
+        if (READ_Y) v = Semi<DT>::add(y[r0 + first_row], v);
+        y[r0 + first_row] = v;
+    }
+    if (tid == MP_THREADS - 1) {  // tile carry-out: partial of the row left open
+        const bool has_items = tile_rows > 0 ? (nz1 > rowend[tile_rows - 1]) : (tile_nnz > 0);
+        int k = tid;
+        while (k > 0 && sm.crow[k - 1] == tile_rows) k--;
+        uint64_t c = sm.cval[k];
+        for (int q = k + 1; q <= tid; q++) c = Semi<DT>::add(c, sm.cval[q]);
+        carry_row[t] = has_items ? r1 : NO_ROW;
+        carry_val[t] = c;
+    }
+}
+
 // Carries of rows that straddle tiles: the head of each run of equal carry rows adds the run
 // (in tile order) to y.  Runs after spmv_merge_kernel on the same stream.
 template <int DT>
@@ -299,8 +450,13 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
             const uint32_t *trow = m.tile_row + tb + sl, *tnz = m.tile_nz + tb + sl;
             uint32_t *crow = m.carry_row + tb;
             uint64_t *cval = (uint64_t *)m.carry_val + tb;
-#define B2_LAUNCH_MERGE(P, R) \
-    spmv_merge_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval)
+#define B2_LAUNCH_MERGE(P, R)                                                                                      \
+    do {                                                                                                           \
+        if (ctx->opt_kernel == 1)                                                                                  \
+            spmv_merge_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval); \
+        else                                                                                                       \
+            spmv_merge_tma_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval); \
+    } while (0)
             const bool prof = ctx->opt_profile && ctx->prof_n + 2 <= 128;
             if (prof) {
                 if (!ctx->prof_ev[ctx->prof_n]) { cudaEventCreate(&ctx->prof_ev[ctx->prof_n]); cudaEventCreate(&ctx->prof_ev[ctx->prof_n + 1]); }
@@ -340,7 +496,11 @@ int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s)
     cudaFuncSetAttribute(spmv_merge_kernel<DT, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
     cudaFuncSetAttribute(spmv_merge_kernel<DT, true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
     cudaFuncSetAttribute(spmv_merge_kernel<DT, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
-    cudaFuncSetAttribute(spmv_merge_kernel<DT, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    cudaFuncSetAttribute(spmv_merge_kernel<DT, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
+    cudaFuncSetAttribute(spmv_merge_tma_kernel<DT, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
+    cudaFuncSetAttribute(spmv_merge_tma_kernel<DT, true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
+    cudaFuncSetAttribute(spmv_merge_tma_kernel<DT, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
+    cudaFuncSetAttribute(spmv_merge_tma_kernel<DT, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         B2_CARVE(B200SPMV_F64)
         B2_CARVE(B200SPMV_U64)
 #undef B2_CARVE

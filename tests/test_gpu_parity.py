@@ -25,9 +25,11 @@ def b2():
     return b200spmv
 
 
-@pytest.fixture()
-def eng(b2):
+@pytest.fixture(params=[2, 1], ids=["tma", "ldg"])
+def eng(b2, request):
+    """both merge-path kernels: 2 = TMA-staged (default), 1 = LDG-staged"""
     e = b2.Engine(0)
+    e.set_option("kernel", request.param)
     yield e
     e.close()
 
