@@ -20,6 +20,7 @@ static void release_matrix(b200spmv_ctx *ctx)
     b2_free(m.rowptr); b2_free(m.colind);
     { uint64_t *v = (uint64_t *)m.vals; b2_free(v); m.vals = nullptr; }
     b2_free(m.tile_row); b2_free(m.tile_nz); b2_free(m.carry_row);
+    b2_free(m.seg_row); b2_free(m.tile_seg);
     { uint64_t *v = (uint64_t *)m.carry_val; b2_free(v); m.carry_val = nullptr; }
     b2_free(ctx->csc_colptr); b2_free(ctx->csc_rowind);
     { uint64_t *v = (uint64_t *)ctx->csc_vals; b2_free(v); ctx->csc_vals = nullptr; }
@@ -88,7 +89,7 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "persist_bytes") ctx->opt_persist_bytes = value;
     else if (k == "require_aligned") ctx->opt_require_aligned = (int)value;
     else if (k == "keep_csc") ctx->opt_keep_csc = (int)value;
-    else if (k == "kernel") { if (value != 1 && value != 2) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 1 or 2"); ctx->opt_kernel = (int)value; }
+    else if (k == "kernel") { if (value < 1 || value > 3) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 1, 2 or 3"); ctx->opt_kernel = (int)value; }
     else if (k == "profile") { ctx->opt_profile = (int)value; ctx->merge_kernel_ns = 0; ctx->merge_kernel_launches = 0; ctx->prof_n = 0; }
     else return b2_fail(ctx, B200SPMV_EINVAL, "unknown option");
     return 0;
@@ -114,21 +115,34 @@ static int csc_to_csr(b200spmv_ctx *ctx, uint32_t index_mask)
     ctx->slab_cols = (uint32_t)(((uint64_t)b2_div_up(ctx->cols, ctx->slabs) + 31) & ~31ull);
     ctx->slabs = (int)b2_div_up(ctx->cols, ctx->slab_cols);
     ctx->rowptr_stride = ((size_t)ctx->local_rows + 1 + 3) & ~(size_t)3;
-    B2_TRY(b2_alloc(ctx, &m.rowptr, ctx->rowptr_stride * ctx->slabs));
-    B2_TRY(b2_alloc(ctx, &m.colind, ctx->local_nnz));
-    { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->local_nnz)); m.vals = v; }
-    // zero the pad so over-reads past the last entry see column 0 / value 0
-    B2_CHECK(ctx, cudaMemsetAsync(m.colind + ctx->local_nnz, 0, 256, s));
-    B2_CHECK(ctx, cudaMemsetAsync((uint64_t *)m.vals + ctx->local_nnz, 0, 256, s));
+    // slab entry ranges in the CSC (columns are contiguous there), each padded to a whole number
+    // of flagged-kernel tiles plus at least one pad entry (the sentinel that closes the last row)
+    std::vector<uint32_t> e0(ctx->slabs), e1(ctx->slabs);
+    uint64_t off = 0;
     for (int sl = 0; sl < ctx->slabs; sl++) {
         const uint32_t c0 = (uint32_t)std::min<uint64_t>((uint64_t)sl * ctx->slab_cols, ctx->cols);
         const uint32_t c1 = (uint32_t)std::min<uint64_t>((uint64_t)c0 + ctx->slab_cols, ctx->cols);
-        uint32_t e0 = 0, e1 = 0;
-        B2_CHECK(ctx, cudaMemcpy(&e0, ctx->csc_colptr + c0, 4, cudaMemcpyDeviceToHost));
-        B2_CHECK(ctx, cudaMemcpy(&e1, ctx->csc_colptr + c1, 4, cudaMemcpyDeviceToHost));
-        B2_TRY(b2_compress(ctx, ctx->local_rows, (uint64_t)e1 - e0, ctx->csc_rowind + e0, index_mask, ctx->row_begin,
-                           ctx->csc_colptr, ctx->cols, e0, nullptr, (const uint64_t *)ctx->csc_vals + e0,
-                           m.rowptr + sl * ctx->rowptr_stride, e0, m.colind + e0, (uint64_t *)m.vals + e0, s));
+        B2_CHECK(ctx, cudaMemcpy(&e0[sl], ctx->csc_colptr + c0, 4, cudaMemcpyDeviceToHost));
+        B2_CHECK(ctx, cudaMemcpy(&e1[sl], ctx->csc_colptr + c1, 4, cudaMemcpyDeviceToHost));
+        ctx->h_slab_off[sl] = off;
+        ctx->h_slab_nnz[sl] = e1[sl] - e0[sl];
+        off += ((uint64_t)(e1[sl] - e0[sl]) + B2_FLAG_TILE) / B2_FLAG_TILE * B2_FLAG_TILE;
+    }
+    ctx->h_slab_off[ctx->slabs] = off;
+    ctx->padded_nnz = off;
+    if (off >= (1ull << 32)) return b2_fail(ctx, B200SPMV_EINVAL, "padded entry count must stay below 2^32");
+    B2_TRY(b2_alloc(ctx, &m.rowptr, ctx->rowptr_stride * ctx->slabs));
+    B2_TRY(b2_alloc(ctx, &m.colind, off));
+    { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, off)); m.vals = v; }
+    // pads (between slabs and after the last entry) read as column 0 / value 0
+    B2_CHECK(ctx, cudaMemsetAsync(m.colind, 0, off * 4 + 256, s));
+    B2_CHECK(ctx, cudaMemsetAsync(m.vals, 0, off * 8 + 256, s));
+    for (int sl = 0; sl < ctx->slabs; sl++) {
+        const uint32_t o = (uint32_t)ctx->h_slab_off[sl];
+        B2_TRY(b2_compress(ctx, ctx->local_rows, (uint64_t)e1[sl] - e0[sl], ctx->csc_rowind + e0[sl], index_mask,
+                           ctx->row_begin, ctx->csc_colptr, ctx->cols, e0[sl], nullptr,
+                           (const uint64_t *)ctx->csc_vals + e0[sl], m.rowptr + sl * ctx->rowptr_stride, o,
+                           m.colind + o, (uint64_t *)m.vals + o, s));
     }
     B2_CHECK(ctx, cudaStreamSynchronize(s));
     ctx->transposetime_ns = now_ns() - t0;
@@ -137,6 +151,7 @@ static int csc_to_csr(b200spmv_ctx *ctx, uint32_t index_mask)
         uint64_t *v = (uint64_t *)ctx->csc_vals; b2_free(v); ctx->csc_vals = nullptr;
     }
     B2_TRY(b2_build_tiles(ctx));
+    B2_TRY(b2_build_flags(ctx));
     { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->cols)); ctx->d_x = v; }
     { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->rows)); ctx->d_y = v; }
     B2_CHECK(ctx, cudaMemsetAsync(ctx->d_x, 0, (size_t)ctx->cols * 8, s));
@@ -307,8 +322,8 @@ extern "C" int b200spmv_get_csr(b200spmv_ctx *ctx, uint32_t *rowptr, uint32_t *c
 {
     B2_NEED_READY(ctx);
     const size_t st = ctx->rowptr_stride;
-    std::vector<uint32_t> rp(st * ctx->slabs), ci(ctx->local_nnz);
-    std::vector<uint64_t> v(ctx->local_nnz);
+    std::vector<uint32_t> rp(st * ctx->slabs), ci(ctx->padded_nnz);
+    std::vector<uint64_t> v(ctx->padded_nnz);
     B2_CHECK(ctx, cudaMemcpy(rp.data(), ctx->csr.rowptr, rp.size() * 4, cudaMemcpyDeviceToHost));
     B2_CHECK(ctx, cudaMemcpy(ci.data(), ctx->csr.colind, ci.size() * 4, cudaMemcpyDeviceToHost));
     B2_CHECK(ctx, cudaMemcpy(v.data(), ctx->csr.vals, v.size() * 8, cudaMemcpyDeviceToHost));
@@ -317,7 +332,7 @@ extern "C" int b200spmv_get_csr(b200spmv_ctx *ctx, uint32_t *rowptr, uint32_t *c
         rowptr[r] = p;
         for (int sl = 0; sl < ctx->slabs; sl++)
             for (uint32_t q = rp[sl * st + r]; q < rp[sl * st + r + 1]; q++) {
-                colind[p] = ci[q];
+                colind[p] = ci[q] & ctx->colmask;
                 ((uint64_t *)vals)[p] = v[q];
                 p++;
             }

@@ -28,6 +28,10 @@ struct DeviceCsr {
     uint32_t *tile_row = nullptr;
     uint32_t *tile_nz = nullptr;
     uint32_t *tile_base = nullptr;  // [slabs+1] first tile of each slab (host copy in h_tile_base)
+    // flagged format (kernel 3): bit 31 of colind marks the first entry of a row; seg_row maps
+    // the n-th non-empty row of a slab to its row id; tile_seg[t] = flags before entry t*FLAG_TILE
+    uint32_t *seg_row = nullptr;    // [slabs][rowptr_stride]  (nseg+1 used, last = NO_ROW)
+    uint32_t *tile_seg = nullptr;   // [slabs] tables, slab s at h_ftile_base[s] + s, ntiles_s + 1 entries
     uint32_t *carry_row = nullptr;  // [tiles] row of the tile's carry-out
     void *carry_val = nullptr;      // [tiles] 8-byte partial of that row
 };
@@ -48,7 +52,7 @@ struct b200spmv_ctx {
     int64_t opt_persist_bytes = 0;  // 0 = device max
     int opt_require_aligned = 0;
     int opt_keep_csc = 0;
-    int opt_kernel = 2;           // merge-path kernel: 1 = LDG-staged (v1), 2 = TMA-staged (v2)
+    int opt_kernel = 3;           // 1 = merge-path LDG-staged, 2 = merge-path TMA-staged, 3 = flagged segmented sum
     int opt_profile = 0;          // 1: bracket every merge-kernel launch with events (bench roofline)
 
     // matrix
@@ -63,6 +67,13 @@ struct b200spmv_ctx {
     int slabs = 1;
     uint32_t slab_cols = 0;       // columns per slab (last may be short)
     uint32_t h_tile_base[65] = {0};
+    uint32_t h_ftile_base[65] = {0};   // flagged-kernel tiles per slab (prefix)
+    uint64_t h_slab_off[65] = {0};     // entry offset of each slab in colind/vals (padded to FLAG_TILE)
+    uint32_t h_slab_nnz[64] = {0};
+    uint32_t h_nseg[64] = {0};         // non-empty rows per slab
+    bool flagged = false;              // colind carries row-start flags in bit 31
+    uint32_t colmask = 0xFFFFFFFFu;    // mask that strips the flag
+    uint64_t padded_nnz = 0;
     uint32_t total_tiles = 0;
     DeviceCsr csr;
     // CSC copy (rank-local entries, global ids)
@@ -155,6 +166,8 @@ int b2_compress(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *k
 int b2_add_u32(b200spmv_ctx *ctx, uint32_t *a, uint64_t n, uint32_t add, cudaStream_t s);
 // spmv.cu
 int b2_build_tiles(b200spmv_ctx *ctx);
+int b2_build_flags(b200spmv_ctx *ctx);
+constexpr uint32_t B2_FLAG_TILE = 2048;  // entries per CTA of the flagged kernel; slabs are padded to it
 int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s);
 void b2_profile_collect(b200spmv_ctx *ctx);
 // synth.cu

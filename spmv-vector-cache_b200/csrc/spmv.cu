@@ -71,7 +71,7 @@ spmv_merge_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restric
                   const uint64_t *__restrict__ vals, const uint64_t *__restrict__ x,
                   uint64_t *__restrict__ y, uint32_t rows, const uint32_t *__restrict__ tile_row,
                   const uint32_t *__restrict__ tile_nz, uint32_t *__restrict__ carry_row,
-                  uint64_t *__restrict__ carry_val)
+                  uint64_t *__restrict__ carry_val, uint32_t colmask)
 {
     __shared__ __align__(16) MergeSmem sm;
     const uint32_t t = blockIdx.x;
@@ -95,7 +95,7 @@ spmv_merge_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restric
         const uint4 c = ld_stream_v4(colind + e, pol_stream);
         uint64_t vv[4];
         ld_stream_v4_b64(vals + e, vv);
-        const uint32_t cc[4] = {c.x, c.y, c.z, c.w};
+        const uint32_t cc[4] = {c.x & colmask, c.y & colmask, c.z & colmask, c.w & colmask};
         uint64_t xv[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) xv[k] = (e + k < nz1) ? load_x<PERSIST>(x, cc[k], pol_keep) : 0ull;
@@ -201,7 +201,7 @@ spmv_merge_tma_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__res
                       const uint64_t *__restrict__ vals, const uint64_t *__restrict__ x,
                       uint64_t *__restrict__ y, uint32_t rows, const uint32_t *__restrict__ tile_row,
                       const uint32_t *__restrict__ tile_nz, uint32_t *__restrict__ carry_row,
-                      uint64_t *__restrict__ carry_val)
+                      uint64_t *__restrict__ carry_val, uint32_t colmask)
 {
     __shared__ __align__(128) TmaSmem sm;
     const uint32_t t = blockIdx.x;
@@ -267,7 +267,7 @@ spmv_merge_tma_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__res
     for (int k = 0; k < MP_IPT; k++) {
         const bool is_entry = (diag + k < tile_items) && !((ends >> k) & 1u);
         const uint32_t jk = k - __popc(ends & ((1u << k) - 1u));
-        xv[k] = is_entry ? load_x<PERSIST>(x, sm.col[off + jk], pol_keep) : 0ull;
+        xv[k] = is_entry ? load_x<PERSIST>(x, sm.col[off + jk] & colmask, pol_keep) : 0ull;
     }
     // pass 3: accumulate in merge order
     uint64_t acc = 0, first_val = 0;
@@ -318,6 +318,183 @@ spmv_merge_tma_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__res
     }
 }
 
+// ---- kernel 3: flagged segmented sum -------------------------------------------------------
+// The CSR built at setup carries a row-start flag in bit 31 of every row's first column index,
+// and each slab's entries are padded to whole tiles (the first pad entry is flagged: it closes
+// the last row).  Stored entries are then split EXACTLY evenly: every thread owns 8 consecutive
+// entries, loaded with 256-bit loads straight into registers (one 32-byte sector of indices,
+// two of values), gathers its 8 x elements, and sums them sequentially, cutting at the flags.
+// Threads are stitched together by a warp-shuffle segmented scan of their open tails, warps
+// through shared memory, tiles through the carry arrays + spmv_fixup_kernel.  No row pointers are
+// read: seg_row[] (only when a slab has empty rows) maps the n-th flag to its row.
+// This is the merge-path idea (nnz-balanced, rows cut wherever the split falls) with the row
+// search replaced by flags precomputed at setup; it costs ~6x fewer instructions per entry than
+// the searching kernels, which matters because the x gathers leave little issue/LSU headroom.
+constexpr int FK_THREADS = 256;
+constexpr int FK_EPT = 8;  // entries per thread
+static_assert(FK_THREADS * FK_EPT == (int)B2_FLAG_TILE, "tile = threads x entries per thread");
+
+__device__ __forceinline__ void ld256_u32(const void *p, uint32_t (&c)[8])
+{
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]), "=r"(c[4]), "=r"(c[5]), "=r"(c[6]), "=r"(c[7])
+                 : "l"(p));
+}
+
+template <int DT, bool READ_Y, bool HAS_EMPTY>
+__device__ __forceinline__ void store_segment(uint64_t *__restrict__ y, const uint32_t *__restrict__ seg_row,
+                                              uint32_t rows, uint32_t seg, uint64_t v)
+{
+    const uint32_t row = HAS_EMPTY ? __ldg(seg_row + seg) : seg;
+    if (row < rows) {
+        if (READ_Y) v = Semi<DT>::add(y[row], v);
+        y[row] = v;
+    }
+}
+
+template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY>
+__global__ void __launch_bounds__(FK_THREADS, 4)
+spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
+                 const uint64_t *__restrict__ x, uint64_t *__restrict__ y,
+                 const uint32_t *__restrict__ seg_row, uint32_t rows, const uint32_t *__restrict__ tile_seg,
+                 uint32_t *__restrict__ carry_row, uint64_t *__restrict__ carry_val)
+{
+    __shared__ uint32_t s_wcnt[FK_THREADS / 32];
+    __shared__ uint32_t s_wflag[FK_THREADS / 32];
+    __shared__ uint64_t s_wsum[FK_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t t = blockIdx.x;
+    const uint64_t pos = (uint64_t)t * B2_FLAG_TILE + (uint64_t)tid * FK_EPT;  // colind/vals are slab-relative
+
+    uint32_t c[FK_EPT];
+    ld256_u32(colind + pos, c);
+    uint64_t v[FK_EPT];
+    {
+        uint64_t a[4], b[4];
+        ld_stream_v4_b64(vals + pos, a);
+        ld_stream_v4_b64(vals + pos + 4, b);
+#pragma unroll
+        for (int i = 0; i < 4; i++) { v[i] = a[i]; v[4 + i] = b[i]; }
+    }
+    const uint64_t pol_keep = policy_evict_last();
+    uint64_t xv[FK_EPT];
+#pragma unroll
+    for (int i = 0; i < FK_EPT; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
+
+    // flags of my entries, and how many segments start before my first entry
+    uint32_t f = 0;
+#pragma unroll
+    for (int i = 0; i < FK_EPT; i++) f |= (c[i] >> 31) << i;
+    const uint32_t nfl = __popc(f);
+    uint32_t incl = nfl;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += n;
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, nfl != 0);
+    if (lane == 31) s_wcnt[warp] = incl;
+    __syncthreads();
+    uint32_t segs_before = __ldg(tile_seg + t) + incl - nfl, tile_flags = 0;
+#pragma unroll
+    for (int w = 0; w < FK_THREADS / 32; w++) {
+        const uint32_t n = s_wcnt[w];
+        if (w < warp) segs_before += n;
+        tile_flags += n;
+    }
+
+    // sequential segmented sum of my 8 products
+    uint64_t acc = 0, head = 0;
+    uint32_t k = 0;
+#pragma unroll
+    for (int i = 0; i < FK_EPT; i++) {
+        if ((f >> i) & 1u) {
+            if (k == 0) head = acc;
+            else store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before + k - 1, acc);  // row inside me
+            k++;
+            acc = 0;
+        }
+        acc = Semi<DT>::add(acc, Semi<DT>::mul(v[i], xv[i]));
+    }
+    // acc = my open tail.  Segmented inclusive scan over the warp: S = sum of tails from the
+    // nearest flagged lane at or below me (or lane 0) to me.
+    const uint32_t below = bal & ((2u << lane) - 1u);  // flagged lanes <= me
+    const int start = below ? 31 - __clz(below) : 0;
+    uint64_t S = acc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
+        if (lane - d >= start) S = Semi<DT>::add(n, S);
+    }
+    uint64_t carry_in = __shfl_up_sync(0xffffffffu, S, 1);  // open partial ending at lane-1
+    if (lane == 0) carry_in = 0;
+    const bool open_left = (bal & ((1u << lane) - 1u)) == 0;  // no flagged lane below me in this warp
+    if (lane == 31) { s_wsum[warp] = S; s_wflag[warp] = bal != 0; }
+    __syncthreads();
+    // partial carried into this warp: sums of the preceding warps back to the nearest flagged one
+    uint64_t cw = 0;
+    {
+        int w0 = warp;
+        while (w0 > 0) { w0--; if (s_wflag[w0]) break; }
+        if (warp > 0) {
+            cw = s_wsum[w0];
+            for (int w = w0 + 1; w < warp; w++) cw = Semi<DT>::add(cw, s_wsum[w]);
+        }
+    }
+    if (nfl != 0 && segs_before != 0) {  // my first flag closes the row that was open on entry
+        uint64_t val = open_left ? Semi<DT>::add(cw, carry_in) : carry_in;
+        val = Semi<DT>::add(val, head);
+        store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before - 1, val);
+    }
+    if (tid == FK_THREADS - 1) {  // tile carry-out: the row left open at the end of the tile
+        const uint64_t out = bal ? S : Semi<DT>::add(cw, S);
+        const uint32_t seg_total = __ldg(tile_seg + t) + tile_flags;
+        uint32_t row = NO_ROW;
+        if (seg_total != 0) {
+            row = HAS_EMPTY ? __ldg(seg_row + seg_total - 1) : seg_total - 1;
+            if (row >= rows) row = NO_ROW;
+        }
+        carry_row[t] = row;
+        carry_val[t] = out;
+    }
+}
+
+// ---- setup of the flagged format (once per matrix) ---------------------------------------------
+__global__ void nonempty_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, uint32_t *__restrict__ ne)
+{
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r <= rows) ne[r] = (r < rows && rowptr[r + 1] > rowptr[r]) ? 1u : 0u;
+}
+// segidx = exclusive scan of ne.  Flag each non-empty row's first entry, fill seg_row, flag the
+// first pad entry (sentinel), terminate seg_row with NO_ROW.
+__global__ void set_flags_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ segidx, uint32_t rows,
+                                 uint32_t *__restrict__ colind, uint32_t *__restrict__ seg_row)
+{
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < rows) {
+        const uint32_t b = rowptr[r];
+        if (rowptr[r + 1] > b) { colind[b] |= 0x80000000u; seg_row[segidx[r]] = r; }
+    } else if (r == rows) {
+        colind[rowptr[rows]] |= 0x80000000u;
+        seg_row[segidx[rows]] = NO_ROW;
+    }
+}
+// tile_seg[t] = flags strictly before entry slab_off + t*TILE
+__global__ void tile_seg_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ segidx, uint32_t rows,
+                                uint32_t slab_off, uint32_t ntiles, uint32_t *__restrict__ tile_seg)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > ntiles) return;
+    const uint64_t pos = (uint64_t)slab_off + (uint64_t)t * B2_FLAG_TILE;
+    uint32_t lo = 0, hi = rows + 1;  // first r in [0, rows] with rowptr[r] >= pos, else rows+1
+    while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        if ((uint64_t)rowptr[mid] < pos) lo = mid + 1; else hi = mid;
+    }
+    const uint32_t sentinel = pos > (uint64_t)rowptr[rows] ? 1u : 0u;
+    tile_seg[t] = segidx[min(lo, rows)] + sentinel;
+}
+
 // Carries of rows that straddle tiles: the head of each run of equal carry rows adds the run
 // (in tile order) to y.  Runs after spmv_merge_kernel on the same stream.
 template <int DT>
@@ -339,14 +516,14 @@ template <int DT, bool READ_Y>
 __global__ void __launch_bounds__(256)
 spmv_rowseq_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ colind,
                    const uint64_t *__restrict__ vals, const uint64_t *__restrict__ x,
-                   uint64_t *__restrict__ y, uint32_t rows)
+                   uint64_t *__restrict__ y, uint32_t rows, uint32_t colmask)
 {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= rows) return;
     uint64_t acc = READ_Y ? y[r] : 0ull;
     const uint32_t end = rowptr[r + 1];
     for (uint32_t p = rowptr[r]; p < end; p++)
-        acc = Semi<DT>::add(acc, Semi<DT>::mul(vals[p], x[colind[p]]));  // mul then add, never FMA
+        acc = Semi<DT>::add(acc, Semi<DT>::mul(vals[p], x[colind[p] & colmask]));  // mul then add, never FMA
     y[r] = acc;
 }
 
@@ -388,6 +565,55 @@ int b2_build_tiles(b200spmv_ctx *ctx)
         B2_CHECK(ctx, cudaGetLastError());
     }
     B2_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// Flagged format for kernel 3 (needs bit 31 of the column ids free).
+int b2_build_flags(b200spmv_ctx *ctx)
+{
+    DeviceCsr &m = ctx->csr;
+    cudaStream_t s = ctx->stream;
+    b2_free(m.seg_row); b2_free(m.tile_seg);
+    ctx->flagged = false;
+    ctx->colmask = 0xFFFFFFFFu;
+    if (ctx->cols > 0x80000000u || ctx->local_rows == 0) return 0;  // kernels 1/2 only
+    const uint32_t rows = ctx->local_rows;
+    const size_t stride = ctx->rowptr_stride;
+    uint32_t total = 0;
+    for (int sl = 0; sl < ctx->slabs; sl++) {
+        ctx->h_ftile_base[sl] = total;
+        total += (uint32_t)((ctx->h_slab_off[sl + 1] - ctx->h_slab_off[sl]) / B2_FLAG_TILE);
+    }
+    ctx->h_ftile_base[ctx->slabs] = total;
+    B2_TRY(b2_alloc(ctx, &m.seg_row, stride * ctx->slabs));
+    B2_TRY(b2_alloc(ctx, &m.tile_seg, (size_t)total + ctx->slabs));
+    if (total > ctx->total_tiles) {  // the carry arrays serve both kernels
+        b2_free(m.carry_row);
+        { uint64_t *cv = (uint64_t *)m.carry_val; b2_free(cv); m.carry_val = nullptr; }
+        B2_TRY(b2_alloc(ctx, &m.carry_row, (size_t)total + 1));
+        uint64_t *cv = nullptr;
+        B2_TRY(b2_alloc(ctx, &cv, (size_t)total + 1));
+        m.carry_val = cv;
+    }
+    uint32_t *segidx = nullptr;
+    B2_TRY(b2_alloc(ctx, &segidx, (size_t)rows + 4));
+    int rc = 0;
+    for (int sl = 0; sl < ctx->slabs && rc == 0; sl++) {
+        const uint32_t *rowptr = m.rowptr + sl * stride;
+        nonempty_kernel<<<b2_div_up((uint64_t)rows + 1, 256), 256, 0, s>>>(rowptr, rows, segidx);
+        if ((rc = b2_exclusive_scan_u32(ctx, segidx, (uint64_t)rows + 1, s))) break;
+        set_flags_kernel<<<b2_div_up((uint64_t)rows + 1, 256), 256, 0, s>>>(rowptr, segidx, rows, m.colind, m.seg_row + sl * stride);
+        const uint32_t nt = ctx->h_ftile_base[sl + 1] - ctx->h_ftile_base[sl];
+        tile_seg_kernel<<<b2_div_up((uint64_t)nt + 1, 256), 256, 0, s>>>(rowptr, segidx, rows, (uint32_t)ctx->h_slab_off[sl], nt,
+                                                                        m.tile_seg + ctx->h_ftile_base[sl] + sl);
+        cudaError_t e = cudaMemcpyAsync(&ctx->h_nseg[sl], segidx + rows, 4, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; rc = B200SPMV_ECUDA; }
+    }
+    cudaFree(segidx);
+    if (rc) return rc;
+    ctx->flagged = true;
+    ctx->colmask = 0x7FFFFFFFu;
     return 0;
 }
 
@@ -438,10 +664,38 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
             B2_TRY(set_persist_window(ctx, s, x + c0, (c1 - c0) * 8, persist));
             ctx->persist_set = persist;
         }
-        if (strict) {
+        if (!strict && ctx->opt_kernel == 3 && ctx->flagged) {
+            const uint32_t tb = ctx->h_ftile_base[sl];
+            const uint32_t nt = ctx->h_ftile_base[sl + 1] - tb;
+            const bool has_empty = ctx->h_nseg[sl] < rows;
+            if (!read_y && has_empty) B2_CHECK(ctx, cudaMemsetAsync(y, 0, (size_t)rows * 8, s));  // rows no flag will touch
+            const uint32_t *ci = m.colind + ctx->h_slab_off[sl];
+            const uint64_t *va = vals + ctx->h_slab_off[sl];
+            const uint32_t *segrow = m.seg_row + sl * stride, *tseg = m.tile_seg + tb + sl;
+            uint32_t *crow = m.carry_row + tb;
+            uint64_t *cval = (uint64_t *)m.carry_val + tb;
+            const bool prof = ctx->opt_profile && ctx->prof_n + 2 <= 128;
+            if (prof) {
+                if (!ctx->prof_ev[ctx->prof_n]) { cudaEventCreate(&ctx->prof_ev[ctx->prof_n]); cudaEventCreate(&ctx->prof_ev[ctx->prof_n + 1]); }
+                cudaEventRecord(ctx->prof_ev[ctx->prof_n], s);
+            }
+#define B2_LAUNCH_FLAG(P, R, E) \
+    spmv_flag_kernel<DT, P, R, E><<<nt, FK_THREADS, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval)
+            if (persist) {
+                if (read_y) { if (has_empty) B2_LAUNCH_FLAG(true, true, true); else B2_LAUNCH_FLAG(true, true, false); }
+                else { if (has_empty) B2_LAUNCH_FLAG(true, false, true); else B2_LAUNCH_FLAG(true, false, false); }
+            } else {
+                if (read_y) { if (has_empty) B2_LAUNCH_FLAG(false, true, true); else B2_LAUNCH_FLAG(false, true, false); }
+                else { if (has_empty) B2_LAUNCH_FLAG(false, false, true); else B2_LAUNCH_FLAG(false, false, false); }
+            }
+#undef B2_LAUNCH_FLAG
+            if (prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
+            spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
+            ctx->launches += 2;
+        } else if (strict) {
             const unsigned grid = b2_div_up(rows, 256);
-            if (read_y) spmv_rowseq_kernel<DT, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows);
-            else spmv_rowseq_kernel<DT, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows);
+            if (read_y) spmv_rowseq_kernel<DT, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows, ctx->colmask);
+            else spmv_rowseq_kernel<DT, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows, ctx->colmask);
             ctx->launches += 1;
         } else {
             const uint32_t tb = ctx->h_tile_base[sl];
@@ -453,9 +707,9 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
 #define B2_LAUNCH_MERGE(P, R)                                                                                      \
     do {                                                                                                           \
         if (ctx->opt_kernel == 1)                                                                                  \
-            spmv_merge_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval); \
+            spmv_merge_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval, ctx->colmask); \
         else                                                                                                       \
-            spmv_merge_tma_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval); \
+            spmv_merge_tma_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval, ctx->colmask); \
     } while (0)
             const bool prof = ctx->opt_profile && ctx->prof_n + 2 <= 128;
             if (prof) {
@@ -471,7 +725,7 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
         }
         B2_CHECK(ctx, cudaGetLastError());
     }
-    ctx->last_mode = strict ? 0 : 1;
+    ctx->last_mode = strict ? 0 : ((ctx->opt_kernel == 3 && ctx->flagged) ? 3 : ctx->opt_kernel);
     return 0;
 }
 

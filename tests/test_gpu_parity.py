@@ -25,9 +25,9 @@ def b2():
     return b200spmv
 
 
-@pytest.fixture(params=[2, 1], ids=["tma", "ldg"])
+@pytest.fixture(params=[3, 2, 1], ids=["flag", "tma", "ldg"])
 def eng(b2, request):
-    """both merge-path kernels: 2 = TMA-staged (default), 1 = LDG-staged"""
+    """all throughput kernels: 3 = flagged segmented sum (default), 2 = merge-path TMA-staged, 1 = merge-path LDG-staged"""
     e = b2.Engine(0)
     e.set_option("kernel", request.param)
     yield e
