@@ -183,6 +183,8 @@ def run_ours(args):
         eng.set_option("slabs", args.slabs)
     if args.kernel:
         eng.set_option("kernel", args.kernel)
+    if args.ept:
+        eng.set_option("ept", args.ept)
     t0 = time.perf_counter()
     eng.setup_synthetic(kind, rows, cols, npr, SEED, b2.F64)
     setup_s = time.perf_counter() - t0
@@ -290,6 +292,7 @@ def main():
     ap.add_argument("--workload", default="uniform", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the row count (experiments only)")
     ap.add_argument("--slabs", type=int, default=0)
+    ap.add_argument("--ept", type=int, default=0, help="entries per thread of kernel 3 (8 or 16)")
     ap.add_argument("--kernel", type=int, default=0, help="merge kernel: 1 LDG-staged, 2 TMA-staged (default)")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
     ap.add_argument("--no-persist", action="store_true")

@@ -89,6 +89,7 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "persist_bytes") ctx->opt_persist_bytes = value;
     else if (k == "require_aligned") ctx->opt_require_aligned = (int)value;
     else if (k == "keep_csc") ctx->opt_keep_csc = (int)value;
+    else if (k == "ept") { if (value != 8 && value != 16) return b2_fail(ctx, B200SPMV_EINVAL, "ept must be 8 or 16"); ctx->opt_ept = (int)value; }
     else if (k == "kernel") { if (value < 1 || value > 3) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 1, 2 or 3"); ctx->opt_kernel = (int)value; }
     else if (k == "profile") { ctx->opt_profile = (int)value; ctx->merge_kernel_ns = 0; ctx->merge_kernel_launches = 0; ctx->prof_n = 0; }
     else return b2_fail(ctx, B200SPMV_EINVAL, "unknown option");

@@ -53,6 +53,7 @@ struct b200spmv_ctx {
     int opt_require_aligned = 0;
     int opt_keep_csc = 0;
     int opt_kernel = 3;           // 1 = merge-path LDG-staged, 2 = merge-path TMA-staged, 3 = flagged segmented sum
+    int opt_ept = 8;              // entries per thread of kernel 3 (8 or 16)
     int opt_profile = 0;          // 1: bracket every merge-kernel launch with events (bench roofline)
 
     // matrix
@@ -208,7 +209,7 @@ __device__ __forceinline__ uint4 ld_stream_v4(const void *p, uint64_t pol)
 // streaming 256-bit load (Blackwell): four 8-byte values, 32-byte aligned
 __device__ __forceinline__ void ld_stream_v4_b64(const void *p, uint64_t (&v)[4])
 {
-    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
+    asm volatile("ld.global.nc.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
                  : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
                  : "l"(p));
 }

@@ -331,13 +331,20 @@ spmv_merge_tma_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__res
 // search replaced by flags precomputed at setup; it costs ~6x fewer instructions per entry than
 // the searching kernels, which matters because the x gathers leave little issue/LSU headroom.
 constexpr int FK_THREADS = 256;
-constexpr int FK_EPT = 8;  // entries per thread
-static_assert(FK_THREADS * FK_EPT == (int)B2_FLAG_TILE, "tile = threads x entries per thread");
+constexpr int FK_WARPS = FK_THREADS / 32;
 
-__device__ __forceinline__ void ld256_u32(const void *p, uint32_t (&c)[8])
+// 8 consecutive u32 / u64 with 256-bit loads.  L1 allocation stays on: a 256-bit load reaches L2
+// as two 128-bit requests for the same 32-byte sector and only an L1 line lets the second merge.
+__device__ __forceinline__ void ld256_u32(const void *p, uint32_t *c)
 {
-    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+    asm volatile("ld.global.nc.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]), "=r"(c[4]), "=r"(c[5]), "=r"(c[6]), "=r"(c[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ void ld256_u64(const void *p, uint64_t *v)
+{
+    asm volatile("ld.global.nc.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3])
                  : "l"(p));
 }
 
@@ -352,73 +359,82 @@ __device__ __forceinline__ void store_segment(uint64_t *__restrict__ y, const ui
     }
 }
 
-template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY>
-__global__ void __launch_bounds__(FK_THREADS, 4)
+// EPT = consecutive entries per thread (8 or 16); the tile is always B2_FLAG_TILE entries, so the
+// CTA has B2_FLAG_TILE / EPT threads.
+template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, int EPT>
+__global__ void __launch_bounds__(B2_FLAG_TILE / EPT, EPT == 8 ? 4 : 4)
 spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
                  const uint64_t *__restrict__ x, uint64_t *__restrict__ y,
                  const uint32_t *__restrict__ seg_row, uint32_t rows, const uint32_t *__restrict__ tile_seg,
                  uint32_t *__restrict__ carry_row, uint64_t *__restrict__ carry_val)
 {
-    __shared__ uint32_t s_wcnt[FK_THREADS / 32];
-    __shared__ uint32_t s_wflag[FK_THREADS / 32];
-    __shared__ uint64_t s_wsum[FK_THREADS / 32];
+    constexpr int THREADS = B2_FLAG_TILE / EPT, WARPS = THREADS / 32;
+    __shared__ uint32_t s_wcnt[WARPS];
+    __shared__ uint32_t s_wflag[WARPS];
+    __shared__ uint64_t s_wsum[WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t t = blockIdx.x;
-    const uint64_t pos = (uint64_t)t * B2_FLAG_TILE + (uint64_t)tid * FK_EPT;  // colind/vals are slab-relative
+    const uint64_t pos = (uint64_t)t * B2_FLAG_TILE + (uint64_t)tid * EPT;  // colind/vals are slab-relative
 
-    uint32_t c[FK_EPT];
-    ld256_u32(colind + pos, c);
-    uint64_t v[FK_EPT];
-    {
-        uint64_t a[4], b[4];
-        ld_stream_v4_b64(vals + pos, a);
-        ld_stream_v4_b64(vals + pos + 4, b);
+    uint32_t c[EPT];
+    uint64_t p[EPT];  // values, then products
 #pragma unroll
-        for (int i = 0; i < 4; i++) { v[i] = a[i]; v[4 + i] = b[i]; }
-    }
+    for (int g = 0; g < EPT / 8; g++) ld256_u32(colind + pos + 8 * g, c + 8 * g);
+#pragma unroll
+    for (int g = 0; g < EPT / 4; g++) ld256_u64(vals + pos + 4 * g, p + 4 * g);
     const uint64_t pol_keep = policy_evict_last();
-    uint64_t xv[FK_EPT];
+    uint64_t xv[EPT];
 #pragma unroll
-    for (int i = 0; i < FK_EPT; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
+    for (int i = 0; i < EPT; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
 
-    // flags of my entries, and how many segments start before my first entry
+    // row-start flags of my entries
     uint32_t f = 0;
 #pragma unroll
-    for (int i = 0; i < FK_EPT; i++) f |= (c[i] >> 31) << i;
+    for (int i = 0; i < EPT; i++) f |= (c[i] >> 31) << i;
     const uint32_t nfl = __popc(f);
-    uint32_t incl = nfl;
+    const uint32_t lt = (1u << lane) - 1u;
+    // flags in lower lanes: sum over the bits of nfl of ballots (no dependent shuffle chain)
+    uint32_t lane_prefix = 0, warp_flags = 0;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t n = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += n;
+    for (int bit = 0; (1 << bit) <= EPT; bit++) {
+        const uint32_t bal_b = __ballot_sync(0xffffffffu, (nfl >> bit) & 1u);
+        lane_prefix += __popc(bal_b & lt) << bit;
+        warp_flags += __popc(bal_b) << bit;
     }
     const uint32_t bal = __ballot_sync(0xffffffffu, nfl != 0);
-    if (lane == 31) s_wcnt[warp] = incl;
-    __syncthreads();
-    uint32_t segs_before = __ldg(tile_seg + t) + incl - nfl, tile_flags = 0;
+    if (lane == 31) s_wcnt[warp] = warp_flags;
+    __syncthreads();  // flag counts only: cheap, and everything below overlaps the gathers in flight
+    uint32_t segs_before = __ldg(tile_seg + t) + lane_prefix, tile_flags = 0;
 #pragma unroll
-    for (int w = 0; w < FK_THREADS / 32; w++) {
+    for (int w = 0; w < WARPS; w++) {
         const uint32_t n = s_wcnt[w];
         if (w < warp) segs_before += n;
         tile_flags += n;
     }
-
-    // sequential segmented sum of my 8 products
-    uint64_t acc = 0, head = 0;
-    uint32_t k = 0;
-#pragma unroll
-    for (int i = 0; i < FK_EPT; i++) {
-        if ((f >> i) & 1u) {
-            if (k == 0) head = acc;
-            else store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before + k - 1, acc);  // row inside me
-            k++;
-            acc = 0;
-        }
-        acc = Semi<DT>::add(acc, Semi<DT>::mul(v[i], xv[i]));
+    // the row my first flag closes, and its current y (accumulate mode): fetched now, needed last
+    uint32_t close_row = NO_ROW;
+    uint64_t y_old = 0;
+    if (nfl != 0 && segs_before != 0) {
+        close_row = HAS_EMPTY ? __ldg(seg_row + segs_before - 1) : segs_before - 1;
+        if (close_row >= rows) close_row = NO_ROW;
+        if (READ_Y && close_row != NO_ROW) y_old = y[close_row];
     }
-    // acc = my open tail.  Segmented inclusive scan over the warp: S = sum of tails from the
-    // nearest flagged lane at or below me (or lane 0) to me.
-    const uint32_t below = bal & ((2u << lane) - 1u);  // flagged lanes <= me
+
+    // branch-free sequential pass: head = sum before my first flag, acc = sum after my last flag
+    uint64_t acc = 0, head = 0;
+    uint32_t seen = 0;
+#pragma unroll
+    for (int i = 0; i < EPT; i++) {
+        p[i] = Semi<DT>::mul(p[i], xv[i]);
+        const uint32_t fl = (f >> i) & 1u;
+        head = (fl & ~seen & 1u) ? acc : head;
+        seen |= fl;
+        acc = fl ? 0ull : acc;
+        acc = Semi<DT>::add(acc, p[i]);
+    }
+    // segmented inclusive scan of the open tails over the warp: S = sum of tails from the nearest
+    // flagged lane at or below me (or lane 0) to me
+    const uint32_t below = bal & ((2u << lane) - 1u);
     const int start = below ? 31 - __clz(below) : 0;
     uint64_t S = acc;
 #pragma unroll
@@ -428,25 +444,40 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
     }
     uint64_t carry_in = __shfl_up_sync(0xffffffffu, S, 1);  // open partial ending at lane-1
     if (lane == 0) carry_in = 0;
-    const bool open_left = (bal & ((1u << lane) - 1u)) == 0;  // no flagged lane below me in this warp
+    const bool open_left = (bal & lt) == 0;  // no flagged lane below me in this warp
     if (lane == 31) { s_wsum[warp] = S; s_wflag[warp] = bal != 0; }
     __syncthreads();
+
     // partial carried into this warp: sums of the preceding warps back to the nearest flagged one
     uint64_t cw = 0;
-    {
-        int w0 = warp;
-        while (w0 > 0) { w0--; if (s_wflag[w0]) break; }
-        if (warp > 0) {
-            cw = s_wsum[w0];
-            for (int w = w0 + 1; w < warp; w++) cw = Semi<DT>::add(cw, s_wsum[w]);
+    if (warp > 0) {
+        int w0 = warp - 1;
+        while (w0 > 0 && !s_wflag[w0]) w0--;
+        cw = s_wsum[w0];
+        for (int w = w0 + 1; w < warp; w++) cw = Semi<DT>::add(cw, s_wsum[w]);
+    }
+    if (nfl != 0) {
+        if (close_row != NO_ROW) {  // my first flag closes the row that was open on entry
+            uint64_t val = open_left ? Semi<DT>::add(cw, carry_in) : carry_in;
+            val = Semi<DT>::add(val, head);
+            if (READ_Y) val = Semi<DT>::add(y_old, val);
+            y[close_row] = val;
+        }
+        if (nfl > 1) {  // rows that begin and end inside my entries (short rows): re-walk
+            uint64_t a = 0;
+            uint32_t k = 0;
+#pragma unroll
+            for (int i = 0; i < EPT; i++) {
+                if ((f >> i) & 1u) {
+                    if (k != 0) store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before + k - 1, a);
+                    k++;
+                    a = 0;
+                }
+                a = Semi<DT>::add(a, p[i]);
+            }
         }
     }
-    if (nfl != 0 && segs_before != 0) {  // my first flag closes the row that was open on entry
-        uint64_t val = open_left ? Semi<DT>::add(cw, carry_in) : carry_in;
-        val = Semi<DT>::add(val, head);
-        store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before - 1, val);
-    }
-    if (tid == FK_THREADS - 1) {  // tile carry-out: the row left open at the end of the tile
+    if (tid == THREADS - 1) {  // tile carry-out: the row left open at the end of the tile
         const uint64_t out = bal ? S : Semi<DT>::add(cw, S);
         const uint32_t seg_total = __ldg(tile_seg + t) + tile_flags;
         uint32_t row = NO_ROW;
@@ -679,8 +710,13 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
                 if (!ctx->prof_ev[ctx->prof_n]) { cudaEventCreate(&ctx->prof_ev[ctx->prof_n]); cudaEventCreate(&ctx->prof_ev[ctx->prof_n + 1]); }
                 cudaEventRecord(ctx->prof_ev[ctx->prof_n], s);
             }
-#define B2_LAUNCH_FLAG(P, R, E) \
-    spmv_flag_kernel<DT, P, R, E><<<nt, FK_THREADS, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval)
+#define B2_LAUNCH_FLAG(P, R, E)                                                                                     \
+    do {                                                                                                           \
+        if (ctx->opt_ept == 16)                                                                                    \
+            spmv_flag_kernel<DT, P, R, E, 16><<<nt, B2_FLAG_TILE / 16, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval); \
+        else                                                                                                       \
+            spmv_flag_kernel<DT, P, R, E, 8><<<nt, B2_FLAG_TILE / 8, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval);  \
+    } while (0)
             if (persist) {
                 if (read_y) { if (has_empty) B2_LAUNCH_FLAG(true, true, true); else B2_LAUNCH_FLAG(true, true, false); }
                 else { if (has_empty) B2_LAUNCH_FLAG(true, false, true); else B2_LAUNCH_FLAG(true, false, false); }

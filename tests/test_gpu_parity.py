@@ -25,11 +25,12 @@ def b2():
     return b200spmv
 
 
-@pytest.fixture(params=[3, 2, 1], ids=["flag", "tma", "ldg"])
+@pytest.fixture(params=[(3, 8), (3, 16), (2, 8), (1, 8)], ids=["flag8", "flag16", "tma", "ldg"])
 def eng(b2, request):
     """all throughput kernels: 3 = flagged segmented sum (default), 2 = merge-path TMA-staged, 1 = merge-path LDG-staged"""
     e = b2.Engine(0)
-    e.set_option("kernel", request.param)
+    e.set_option("kernel", request.param[0])
+    e.set_option("ept", request.param[1])
     yield e
     e.close()
 
