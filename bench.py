@@ -167,7 +167,7 @@ def run_ours(args):
     kind, rows, npr, desc = WORKLOADS[args.workload]
     if args.rows:
         rows = args.rows
-    cols = rows
+    cols = args.cols or rows
     flags = 0 if args.overwrite else b2.ACCUMULATE
     if args.no_persist:
         flags |= b2.NO_PERSIST
@@ -185,6 +185,8 @@ def run_ours(args):
         eng.set_option("kernel", args.kernel)
     if args.ept:
         eng.set_option("ept", args.ept)
+    if args.ctas:
+        eng.set_option("ctas_per_sm", args.ctas)
     t0 = time.perf_counter()
     eng.setup_synthetic(kind, rows, cols, npr, SEED, b2.F64)
     setup_s = time.perf_counter() - t0
@@ -291,9 +293,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="uniform", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the row count (experiments only)")
+    ap.add_argument("--cols", type=int, default=0, help="override the column count (experiments only)")
     ap.add_argument("--slabs", type=int, default=0)
     ap.add_argument("--ept", type=int, default=0, help="entries per thread of kernel 3 (8 or 16)")
-    ap.add_argument("--kernel", type=int, default=0, help="merge kernel: 1 LDG-staged, 2 TMA-staged (default)")
+    ap.add_argument("--kernel", type=int, default=0,
+                    help="1 merge-path LDG-staged, 2 merge-path TMA-staged, 3 flagged, 4 flagged persistent TMA ring (default)")
+    ap.add_argument("--ctas", type=int, default=0, help="persistent CTAs per SM of kernel 4")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
     ap.add_argument("--no-persist", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

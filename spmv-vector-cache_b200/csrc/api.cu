@@ -20,7 +20,7 @@ static void release_matrix(b200spmv_ctx *ctx)
     b2_free(m.rowptr); b2_free(m.colind);
     { uint64_t *v = (uint64_t *)m.vals; b2_free(v); m.vals = nullptr; }
     b2_free(m.tile_row); b2_free(m.tile_nz); b2_free(m.carry_row);
-    b2_free(m.seg_row); b2_free(m.tile_seg);
+    b2_free(m.seg_row); b2_free(m.tile_seg); b2_free(m.warp_seg);
     { uint64_t *v = (uint64_t *)m.carry_val; b2_free(v); m.carry_val = nullptr; }
     b2_free(ctx->csc_colptr); b2_free(ctx->csc_rowind);
     { uint64_t *v = (uint64_t *)ctx->csc_vals; b2_free(v); ctx->csc_vals = nullptr; }
@@ -90,7 +90,8 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "require_aligned") ctx->opt_require_aligned = (int)value;
     else if (k == "keep_csc") ctx->opt_keep_csc = (int)value;
     else if (k == "ept") { if (value != 8 && value != 16) return b2_fail(ctx, B200SPMV_EINVAL, "ept must be 8 or 16"); ctx->opt_ept = (int)value; }
-    else if (k == "kernel") { if (value < 1 || value > 3) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 1, 2 or 3"); ctx->opt_kernel = (int)value; }
+    else if (k == "kernel") { if (value < 1 || value > 5) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 1..5"); ctx->opt_kernel = (int)value; }
+    else if (k == "ctas_per_sm") { if (value < 1 || value > 8) return b2_fail(ctx, B200SPMV_EINVAL, "ctas_per_sm must be 1..8"); ctx->opt_ctas_per_sm = (int)value; }
     else if (k == "profile") { ctx->opt_profile = (int)value; ctx->merge_kernel_ns = 0; ctx->merge_kernel_launches = 0; ctx->prof_n = 0; }
     else return b2_fail(ctx, B200SPMV_EINVAL, "unknown option");
     return 0;

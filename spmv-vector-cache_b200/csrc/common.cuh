@@ -32,6 +32,7 @@ struct DeviceCsr {
     // the n-th non-empty row of a slab to its row id; tile_seg[t] = flags before entry t*FLAG_TILE
     uint32_t *seg_row = nullptr;    // [slabs][rowptr_stride]  (nseg+1 used, last = NO_ROW)
     uint32_t *tile_seg = nullptr;   // [slabs] tables, slab s at h_ftile_base[s] + s, ntiles_s + 1 entries
+    uint32_t *warp_seg = nullptr;   // same per 256-entry warp tile (kernel 5), slab s at 8*h_ftile_base[s] + s
     uint32_t *carry_row = nullptr;  // [tiles] row of the tile's carry-out
     void *carry_val = nullptr;      // [tiles] 8-byte partial of that row
 };
@@ -52,7 +53,9 @@ struct b200spmv_ctx {
     int64_t opt_persist_bytes = 0;  // 0 = device max
     int opt_require_aligned = 0;
     int opt_keep_csc = 0;
-    int opt_kernel = 3;           // 1 = merge-path LDG-staged, 2 = merge-path TMA-staged, 3 = flagged segmented sum
+    int opt_kernel = 3;           // 1 = merge-path LDG-staged, 2 = merge-path TMA-staged, 3 = flagged segmented sum,
+                                  // 4 = flagged, persistent CTAs with a TMA-fed shared-memory ring, 5 = flagged, warp-sized tiles
+    int opt_ctas_per_sm = 4;      // persistent grid of kernel 4 = sms * this
     int opt_ept = 8;              // entries per thread of kernel 3 (8 or 16)
     int opt_profile = 0;          // 1: bracket every merge-kernel launch with events (bench roofline)
 

@@ -490,6 +490,320 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
     }
 }
 
+// ---- kernel 4: persistent flagged segmented sum with a TMA-fed shared-memory ring ------------------
+// Same arithmetic and the same flagged tiles as kernel 3, but the CTAs are persistent (grid = SMs x
+// resident CTAs, tiles dealt round-robin) and the two entry streams of tile i + RING are brought into
+// a shared-memory ring by 1-D bulk async copies (TMA, cp.async.bulk -> UBLKCP) issued by one thread
+// as soon as the ring slot has been read into registers.  What bounds this kernel on a matrix without
+// locality is the rate at which one SM can post L2 requests for the x gathers (ncu:
+// l1tex__m_l1tex2xbar_req_cycles_active, profiles/r01_k3_flag_ncu_summary.txt); kernel 3 leaves that
+// port idle while a fresh CTA waits for its first HBM loads, here the streams are already on chip
+// when a tile starts, so the gathers are issued back to back.
+constexpr int PK_RING = 2;
+constexpr uint32_t PK_STAGE_BYTES = B2_FLAG_TILE * 12u;
+constexpr uint32_t PK_SMEM_BYTES = PK_RING * PK_STAGE_BYTES + 128;  // + full[RING], empty[RING] mbarriers
+
+template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY>
+__global__ void __launch_bounds__(B2_FLAG_TILE / 8, 4)
+spmv_flag_ring_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
+                      const uint64_t *__restrict__ x, uint64_t *__restrict__ y,
+                      const uint32_t *__restrict__ seg_row, uint32_t rows, const uint32_t *__restrict__ tile_seg,
+                      uint32_t *__restrict__ carry_row, uint64_t *__restrict__ carry_val, uint32_t ntiles)
+{
+    constexpr int EPT = 8, THREADS = B2_FLAG_TILE / EPT, WARPS = THREADS / 32;
+    extern __shared__ __align__(128) unsigned char pk_smem[];
+    // slot s: values at s*PK_STAGE_BYTES (16 KB), column indices behind them (8 KB)
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(pk_smem + PK_RING * PK_STAGE_BYTES);
+    __shared__ uint32_t s_wcnt[WARPS];
+    __shared__ uint32_t s_wflag[WARPS];
+    __shared__ uint64_t s_wsum[WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint64_t pol_stream = policy_evict_first(), pol_keep = policy_evict_last();
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < PK_RING; s++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[s])));            // full: producer + tx bytes
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&s_bar[PK_RING + s])), "r"(WARPS));  // empty: one arrival per warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+#pragma unroll
+        for (int s = 0; s < PK_RING; s++) {
+            const uint64_t t = (uint64_t)blockIdx.x + (uint64_t)s * gridDim.x;
+            if (t < ntiles) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&s_bar[s])), "r"(PK_STAGE_BYTES) : "memory");
+                tma_load_1d(pk_smem + s * PK_STAGE_BYTES, vals + t * B2_FLAG_TILE, B2_FLAG_TILE * 8u, &s_bar[s], pol_stream);
+                tma_load_1d(pk_smem + s * PK_STAGE_BYTES + B2_FLAG_TILE * 8u, colind + t * B2_FLAG_TILE, B2_FLAG_TILE * 4u, &s_bar[s], pol_stream);
+            }
+        }
+    }
+    __syncthreads();
+
+    uint32_t it = 0;
+    for (uint64_t t64 = blockIdx.x; t64 < ntiles; t64 += gridDim.x, it++) {
+        const uint32_t t = (uint32_t)t64;
+        const int slot = it % PK_RING;
+        const uint32_t parity = (it / PK_RING) & 1u;
+        const uint32_t tseg = __ldg(tile_seg + t);
+        {
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                             : "=r"(done) : "r"(smem_u32(&s_bar[slot])), "r"(parity) : "memory");
+        }
+        uint32_t c[EPT];
+        uint64_t p[EPT];
+        {
+            const uint4 *sc = reinterpret_cast<const uint4 *>(pk_smem + slot * PK_STAGE_BYTES + B2_FLAG_TILE * 8u) + tid * 2;
+            const uint4 c0 = sc[0], c1 = sc[1];
+            c[0] = c0.x; c[1] = c0.y; c[2] = c0.z; c[3] = c0.w; c[4] = c1.x; c[5] = c1.y; c[6] = c1.z; c[7] = c1.w;
+        }
+        uint64_t xv[EPT];
+#pragma unroll
+        for (int i = 0; i < EPT; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
+        {
+            const ulonglong2 *sv = reinterpret_cast<const ulonglong2 *>(pk_smem + slot * PK_STAGE_BYTES) + tid * 4;
+#pragma unroll
+            for (int g = 0; g < 4; g++) { const ulonglong2 v = sv[g]; p[2 * g] = v.x; p[2 * g + 1] = v.y; }
+        }
+        // release the slot: my reads (generic proxy) are ordered before the refill (async proxy) that
+        // thread 0 issues once every warp has arrived.  (A __syncthreads is not enough here: BAR.SYNC
+        // defers its blocking to the next instruction that touches shared memory, and the bulk copy
+        // is not one.)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_bar[PK_RING + slot])) : "memory");
+
+        uint32_t f = 0;
+#pragma unroll
+        for (int i = 0; i < EPT; i++) f |= (c[i] >> 31) << i;
+        const uint32_t nfl = __popc(f);
+        const uint32_t lt = (1u << lane) - 1u;
+        uint32_t lane_prefix = 0, warp_flags = 0;
+#pragma unroll
+        for (int bit = 0; (1 << bit) <= EPT; bit++) {
+            const uint32_t bal_b = __ballot_sync(0xffffffffu, (nfl >> bit) & 1u);
+            lane_prefix += __popc(bal_b & lt) << bit;
+            warp_flags += __popc(bal_b) << bit;
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, nfl != 0);
+        if (lane == 31) s_wcnt[warp] = warp_flags;
+        __syncthreads();  // (A)
+        if (tid == 0) {
+            const uint64_t tn = t64 + (uint64_t)PK_RING * gridDim.x;
+            if (tn < ntiles) {
+                uint32_t done = 0;  // every warp holds its part of the slot in registers
+                while (!done)
+                    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                                 : "=r"(done) : "r"(smem_u32(&s_bar[PK_RING + slot])), "r"(parity) : "memory");
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&s_bar[slot])), "r"(PK_STAGE_BYTES) : "memory");
+                tma_load_1d(pk_smem + slot * PK_STAGE_BYTES, vals + tn * B2_FLAG_TILE, B2_FLAG_TILE * 8u, &s_bar[slot], pol_stream);
+                tma_load_1d(pk_smem + slot * PK_STAGE_BYTES + B2_FLAG_TILE * 8u, colind + tn * B2_FLAG_TILE, B2_FLAG_TILE * 4u, &s_bar[slot], pol_stream);
+            }
+        }
+        uint32_t segs_before = tseg + lane_prefix, tile_flags = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; w++) {
+            const uint32_t n = s_wcnt[w];
+            if (w < warp) segs_before += n;
+            tile_flags += n;
+        }
+        uint32_t close_row = NO_ROW;
+        uint64_t y_old = 0;
+        if (nfl != 0 && segs_before != 0) {
+            close_row = HAS_EMPTY ? __ldg(seg_row + segs_before - 1) : segs_before - 1;
+            if (close_row >= rows) close_row = NO_ROW;
+            if (READ_Y && close_row != NO_ROW) y_old = y[close_row];
+        }
+
+        uint64_t acc = 0, head = 0;
+        uint32_t seen = 0;
+#pragma unroll
+        for (int i = 0; i < EPT; i++) {
+            p[i] = Semi<DT>::mul(p[i], xv[i]);
+            const uint32_t fl = (f >> i) & 1u;
+            head = (fl & ~seen & 1u) ? acc : head;
+            seen |= fl;
+            acc = fl ? 0ull : acc;
+            acc = Semi<DT>::add(acc, p[i]);
+        }
+        const uint32_t below = bal & ((2u << lane) - 1u);
+        const int start = below ? 31 - __clz(below) : 0;
+        uint64_t S = acc;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
+            if (lane - d >= start) S = Semi<DT>::add(n, S);
+        }
+        uint64_t carry_in = __shfl_up_sync(0xffffffffu, S, 1);
+        if (lane == 0) carry_in = 0;
+        const bool open_left = (bal & lt) == 0;
+        if (lane == 31) { s_wsum[warp] = S; s_wflag[warp] = bal != 0; }
+        __syncthreads();  // (B)
+
+        uint64_t cw = 0;
+        if (warp > 0) {
+            int w0 = warp - 1;
+            while (w0 > 0 && !s_wflag[w0]) w0--;
+            cw = s_wsum[w0];
+            for (int w = w0 + 1; w < warp; w++) cw = Semi<DT>::add(cw, s_wsum[w]);
+        }
+        if (nfl != 0) {
+            if (close_row != NO_ROW) {
+                uint64_t val = open_left ? Semi<DT>::add(cw, carry_in) : carry_in;
+                val = Semi<DT>::add(val, head);
+                if (READ_Y) val = Semi<DT>::add(y_old, val);
+                y[close_row] = val;
+            }
+            if (nfl > 1) {
+                uint64_t a = 0;
+                uint32_t k = 0;
+#pragma unroll
+                for (int i = 0; i < EPT; i++) {
+                    if ((f >> i) & 1u) {
+                        if (k != 0) store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before + k - 1, a);
+                        k++;
+                        a = 0;
+                    }
+                    a = Semi<DT>::add(a, p[i]);
+                }
+            }
+        }
+        if (tid == THREADS - 1) {
+            const uint64_t out = bal ? S : Semi<DT>::add(cw, S);
+            const uint32_t seg_total = tseg + tile_flags;
+            uint32_t row = NO_ROW;
+            if (seg_total != 0) {
+                row = HAS_EMPTY ? __ldg(seg_row + seg_total - 1) : seg_total - 1;
+                if (row >= rows) row = NO_ROW;
+            }
+            carry_row[t] = row;
+            carry_val[t] = out;
+        }
+        // s_wcnt is rewritten before (A) of the next tile and was last read before (B) of this one;
+        // s_wsum / s_wflag are rewritten after (A) of the next tile, which every reader above has passed
+    }
+}
+
+// ---- kernel 5: flagged segmented sum with WARP-sized tiles ------------------------------------------
+// Same flagged streams as kernel 3, but the unit of work is one warp = 256 consecutive entries, and
+// warps never talk to each other: no shared memory, no __syncthreads.  The number of row-start flags
+// before each warp's first entry comes from a table built at setup (warp_seg, 4 bytes per 256 entries),
+// rows that straddle warps go through the carry arrays (one slot per warp) and spmv_fixup_kernel.
+// Why: on a matrix without locality the x gathers queue in the SM's single in-order load pipeline at
+// ~1 wavefront / clk, and every shared-memory round trip or barrier of kernel 3 waits behind that
+// queue once more (ncu: short_scoreboard + barrier + mio stalls = 45 % in
+// profiles/r01_k3_flag_ncu_summary.txt).  Here the only dependent round trips of a warp are
+// streams -> gathers (-> seg_row -> y when the slab has empty rows / accumulates), and the 32 warps
+// resident on an SM are 32 independent chains, so the load pipeline does not run dry.
+constexpr int WK_ENTRIES = 256;  // per warp: 32 lanes x 8 entries
+constexpr int WK_PER_TILE = (int)(B2_FLAG_TILE / WK_ENTRIES);
+
+template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, int OCC>
+__global__ void __launch_bounds__(256, OCC)
+spmv_flag_warp_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
+                      const uint64_t *__restrict__ x, uint64_t *__restrict__ y,
+                      const uint32_t *__restrict__ seg_row, uint32_t rows, const uint32_t *__restrict__ warp_seg,
+                      uint32_t *__restrict__ carry_row, uint64_t *__restrict__ carry_val, uint32_t nwarps)
+{
+    constexpr int EPT = 8;
+    const int lane = threadIdx.x & 31;
+    const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (gw >= nwarps) return;
+    const uint64_t pos = (uint64_t)gw * WK_ENTRIES + (uint64_t)lane * EPT;
+
+    uint32_t c[EPT];
+    uint64_t p[EPT];
+    ld256_u32(colind + pos, c);
+    ld256_u64(vals + pos, p);
+    ld256_u64(vals + pos + 4, p + 4);
+    const uint32_t wbase = __ldg(warp_seg + gw);
+    const uint64_t pol_keep = policy_evict_last();
+    uint64_t xv[EPT];
+#pragma unroll
+    for (int i = 0; i < EPT; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
+
+    uint32_t f = 0;
+#pragma unroll
+    for (int i = 0; i < EPT; i++) f |= (c[i] >> 31) << i;
+    const uint32_t nfl = __popc(f);
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t lane_prefix = 0, warp_flags = 0;
+#pragma unroll
+    for (int bit = 0; (1 << bit) <= EPT; bit++) {
+        const uint32_t bal_b = __ballot_sync(0xffffffffu, (nfl >> bit) & 1u);
+        lane_prefix += __popc(bal_b & lt) << bit;
+        warp_flags += __popc(bal_b) << bit;
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, nfl != 0);
+    const uint32_t segs_before = wbase + lane_prefix;
+    // the row my first flag closes and (accumulate / later slabs) its current y: issued while the
+    // gathers are in flight
+    uint32_t close_row = NO_ROW;
+    uint64_t y_old = 0;
+    if (nfl != 0 && segs_before != 0) {
+        close_row = HAS_EMPTY ? __ldg(seg_row + segs_before - 1) : segs_before - 1;
+        if (close_row >= rows) close_row = NO_ROW;
+        if (READ_Y && close_row != NO_ROW) y_old = y[close_row];
+    }
+
+    uint64_t acc = 0, head = 0;
+    uint32_t seen = 0;
+#pragma unroll
+    for (int i = 0; i < EPT; i++) {
+        p[i] = Semi<DT>::mul(p[i], xv[i]);
+        const uint32_t fl = (f >> i) & 1u;
+        head = (fl & ~seen & 1u) ? acc : head;
+        seen |= fl;
+        acc = fl ? 0ull : acc;
+        acc = Semi<DT>::add(acc, p[i]);
+    }
+    // segmented inclusive scan of the open tails: S = sum from the nearest flagged lane at or below me
+    const uint32_t below = bal & ((2u << lane) - 1u);
+    const int start = below ? 31 - __clz(below) : 0;
+    uint64_t S = acc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
+        if (lane - d >= start) S = Semi<DT>::add(n, S);
+    }
+    uint64_t carry_in = __shfl_up_sync(0xffffffffu, S, 1);
+    if (lane == 0) carry_in = 0;
+
+    if (nfl != 0) {
+        if (close_row != NO_ROW) {
+            // when no lane below me has a flag this is only the warp's share of the row: the shares of
+            // the preceding warps arrive through their carries
+            uint64_t val = Semi<DT>::add(carry_in, head);
+            if (READ_Y) val = Semi<DT>::add(y_old, val);
+            y[close_row] = val;
+        }
+        if (nfl > 1) {
+            uint64_t a = 0;
+            uint32_t k = 0;
+#pragma unroll
+            for (int i = 0; i < EPT; i++) {
+                if ((f >> i) & 1u) {
+                    if (k != 0) store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before + k - 1, a);
+                    k++;
+                    a = 0;
+                }
+                a = Semi<DT>::add(a, p[i]);
+            }
+        }
+    }
+    if (lane == 31) {  // carry-out: the row left open at the end of this warp's entries
+        const uint32_t seg_total = wbase + warp_flags;
+        uint32_t row = NO_ROW;
+        if (seg_total != 0) {
+            row = HAS_EMPTY ? __ldg(seg_row + seg_total - 1) : seg_total - 1;
+            if (row >= rows) row = NO_ROW;
+        }
+        carry_row[gw] = row;
+        carry_val[gw] = S;
+    }
+}
+
 // ---- setup of the flagged format (once per matrix) ---------------------------------------------
 __global__ void nonempty_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, uint32_t *__restrict__ ne)
 {
@@ -512,11 +826,11 @@ __global__ void set_flags_kernel(const uint32_t *__restrict__ rowptr, const uint
 }
 // tile_seg[t] = flags strictly before entry slab_off + t*TILE
 __global__ void tile_seg_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ segidx, uint32_t rows,
-                                uint32_t slab_off, uint32_t ntiles, uint32_t *__restrict__ tile_seg)
+                                uint32_t slab_off, uint32_t ntiles, uint32_t tile, uint32_t *__restrict__ tile_seg)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t > ntiles) return;
-    const uint64_t pos = (uint64_t)slab_off + (uint64_t)t * B2_FLAG_TILE;
+    const uint64_t pos = (uint64_t)slab_off + (uint64_t)t * tile;
     uint32_t lo = 0, hi = rows + 1;  // first r in [0, rows] with rowptr[r] >= pos, else rows+1
     while (lo < hi) {
         const uint32_t mid = lo + ((hi - lo) >> 1);
@@ -604,7 +918,7 @@ int b2_build_flags(b200spmv_ctx *ctx)
 {
     DeviceCsr &m = ctx->csr;
     cudaStream_t s = ctx->stream;
-    b2_free(m.seg_row); b2_free(m.tile_seg);
+    b2_free(m.seg_row); b2_free(m.tile_seg); b2_free(m.warp_seg);
     ctx->flagged = false;
     ctx->colmask = 0xFFFFFFFFu;
     if (ctx->cols > 0x80000000u || ctx->local_rows == 0) return 0;  // kernels 1/2 only
@@ -618,12 +932,13 @@ int b2_build_flags(b200spmv_ctx *ctx)
     ctx->h_ftile_base[ctx->slabs] = total;
     B2_TRY(b2_alloc(ctx, &m.seg_row, stride * ctx->slabs));
     B2_TRY(b2_alloc(ctx, &m.tile_seg, (size_t)total + ctx->slabs));
-    if (total > ctx->total_tiles) {  // the carry arrays serve both kernels
+    B2_TRY(b2_alloc(ctx, &m.warp_seg, (size_t)total * WK_PER_TILE + ctx->slabs));
+    if ((uint64_t)total * WK_PER_TILE > ctx->total_tiles) {  // the carry arrays serve every kernel: one slot per warp tile
         b2_free(m.carry_row);
         { uint64_t *cv = (uint64_t *)m.carry_val; b2_free(cv); m.carry_val = nullptr; }
-        B2_TRY(b2_alloc(ctx, &m.carry_row, (size_t)total + 1));
+        B2_TRY(b2_alloc(ctx, &m.carry_row, (size_t)total * WK_PER_TILE + 1));
         uint64_t *cv = nullptr;
-        B2_TRY(b2_alloc(ctx, &cv, (size_t)total + 1));
+        B2_TRY(b2_alloc(ctx, &cv, (size_t)total * WK_PER_TILE + 1));
         m.carry_val = cv;
     }
     uint32_t *segidx = nullptr;
@@ -636,7 +951,10 @@ int b2_build_flags(b200spmv_ctx *ctx)
         set_flags_kernel<<<b2_div_up((uint64_t)rows + 1, 256), 256, 0, s>>>(rowptr, segidx, rows, m.colind, m.seg_row + sl * stride);
         const uint32_t nt = ctx->h_ftile_base[sl + 1] - ctx->h_ftile_base[sl];
         tile_seg_kernel<<<b2_div_up((uint64_t)nt + 1, 256), 256, 0, s>>>(rowptr, segidx, rows, (uint32_t)ctx->h_slab_off[sl], nt,
-                                                                        m.tile_seg + ctx->h_ftile_base[sl] + sl);
+                                                                        B2_FLAG_TILE, m.tile_seg + ctx->h_ftile_base[sl] + sl);
+        tile_seg_kernel<<<b2_div_up((uint64_t)nt * WK_PER_TILE + 1, 256), 256, 0, s>>>(
+            rowptr, segidx, rows, (uint32_t)ctx->h_slab_off[sl], nt * WK_PER_TILE, WK_ENTRIES,
+            m.warp_seg + (size_t)ctx->h_ftile_base[sl] * WK_PER_TILE + sl);
         cudaError_t e = cudaMemcpyAsync(&ctx->h_nseg[sl], segidx + rows, 4, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess) e = cudaStreamSynchronize(s);
         if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; rc = B200SPMV_ECUDA; }
@@ -695,7 +1013,7 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
             B2_TRY(set_persist_window(ctx, s, x + c0, (c1 - c0) * 8, persist));
             ctx->persist_set = persist;
         }
-        if (!strict && ctx->opt_kernel == 3 && ctx->flagged) {
+        if (!strict && ctx->opt_kernel >= 3 && ctx->flagged) {
             const uint32_t tb = ctx->h_ftile_base[sl];
             const uint32_t nt = ctx->h_ftile_base[sl + 1] - tb;
             const bool has_empty = ctx->h_nseg[sl] < rows;
@@ -717,7 +1035,48 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
         else                                                                                                       \
             spmv_flag_kernel<DT, P, R, E, 8><<<nt, B2_FLAG_TILE / 8, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval);  \
     } while (0)
-            if (persist) {
+#define B2_LAUNCH_RING(P, R, E)                                                                                     \
+    do {                                                                                                           \
+        auto kfn = spmv_flag_ring_kernel<DT, P, R, E>;                                                             \
+        static bool attr_set = false;                                                                              \
+        if (!attr_set) {                                                                                           \
+            B2_CHECK(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PK_SMEM_BYTES)); \
+            B2_CHECK(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));         \
+            attr_set = true;                                                                                       \
+        }                                                                                                          \
+        const uint32_t grid = std::min<uint32_t>(nt, (uint32_t)ctx->sms * (uint32_t)ctx->opt_ctas_per_sm);         \
+        kfn<<<grid, B2_FLAG_TILE / 8, PK_SMEM_BYTES, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval, nt);       \
+    } while (0)
+#define B2_LAUNCH_WARP(P, R, E)                                                                                     \
+    do {                                                                                                           \
+        if (ctx->opt_ctas_per_sm == 5)                                                                             \
+            spmv_flag_warp_kernel<DT, P, R, E, 5><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
+        else if (ctx->opt_ctas_per_sm == 6)                                                                        \
+            spmv_flag_warp_kernel<DT, P, R, E, 6><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
+        else                                                                                                       \
+            spmv_flag_warp_kernel<DT, P, R, E, 4><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
+    } while (0)
+            const uint32_t nw = nt * WK_PER_TILE;
+            const uint32_t *wseg = m.warp_seg + (size_t)tb * WK_PER_TILE + sl;
+            uint32_t *wcrow = m.carry_row + (size_t)tb * WK_PER_TILE;
+            uint64_t *wcval = (uint64_t *)m.carry_val + (size_t)tb * WK_PER_TILE;
+            if (ctx->opt_kernel == 5) {
+                if (persist) {
+                    if (read_y) { if (has_empty) B2_LAUNCH_WARP(true, true, true); else B2_LAUNCH_WARP(true, true, false); }
+                    else { if (has_empty) B2_LAUNCH_WARP(true, false, true); else B2_LAUNCH_WARP(true, false, false); }
+                } else {
+                    if (read_y) { if (has_empty) B2_LAUNCH_WARP(false, true, true); else B2_LAUNCH_WARP(false, true, false); }
+                    else { if (has_empty) B2_LAUNCH_WARP(false, false, true); else B2_LAUNCH_WARP(false, false, false); }
+                }
+            } else if (ctx->opt_kernel == 4) {
+                if (persist) {
+                    if (read_y) { if (has_empty) B2_LAUNCH_RING(true, true, true); else B2_LAUNCH_RING(true, true, false); }
+                    else { if (has_empty) B2_LAUNCH_RING(true, false, true); else B2_LAUNCH_RING(true, false, false); }
+                } else {
+                    if (read_y) { if (has_empty) B2_LAUNCH_RING(false, true, true); else B2_LAUNCH_RING(false, true, false); }
+                    else { if (has_empty) B2_LAUNCH_RING(false, false, true); else B2_LAUNCH_RING(false, false, false); }
+                }
+            } else if (persist) {
                 if (read_y) { if (has_empty) B2_LAUNCH_FLAG(true, true, true); else B2_LAUNCH_FLAG(true, true, false); }
                 else { if (has_empty) B2_LAUNCH_FLAG(true, false, true); else B2_LAUNCH_FLAG(true, false, false); }
             } else {
@@ -725,8 +1084,11 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
                 else { if (has_empty) B2_LAUNCH_FLAG(false, false, true); else B2_LAUNCH_FLAG(false, false, false); }
             }
 #undef B2_LAUNCH_FLAG
+#undef B2_LAUNCH_RING
+#undef B2_LAUNCH_WARP
             if (prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
-            spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
+            if (ctx->opt_kernel == 5) spmv_fixup_kernel<DT><<<b2_div_up(nw, 256), 256, 0, s>>>(wcrow, wcval, nw, y);
+            else spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
             ctx->launches += 2;
         } else if (strict) {
             const unsigned grid = b2_div_up(rows, 256);
@@ -761,7 +1123,7 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
         }
         B2_CHECK(ctx, cudaGetLastError());
     }
-    ctx->last_mode = strict ? 0 : ((ctx->opt_kernel == 3 && ctx->flagged) ? 3 : ctx->opt_kernel);
+    ctx->last_mode = strict ? 0 : ((ctx->opt_kernel >= 3 && !ctx->flagged) ? 2 : ctx->opt_kernel);
     return 0;
 }
 

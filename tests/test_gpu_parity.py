@@ -25,9 +25,11 @@ def b2():
     return b200spmv
 
 
-@pytest.fixture(params=[(3, 8), (3, 16), (2, 8), (1, 8)], ids=["flag8", "flag16", "tma", "ldg"])
+@pytest.fixture(params=[(5, 8), (4, 8), (3, 8), (3, 16), (2, 8), (1, 8)], ids=["warp", "ring", "flag8", "flag16", "tma", "ldg"])
 def eng(b2, request):
-    """all throughput kernels: 3 = flagged segmented sum (default), 2 = merge-path TMA-staged, 1 = merge-path LDG-staged"""
+    """all throughput kernels: 5 = flagged, warp-sized tiles (default), 4 = flagged, persistent CTAs + TMA ring,
+    3 = flagged segmented sum,
+    2 = merge-path TMA-staged, 1 = merge-path LDG-staged"""
     e = b2.Engine(0)
     e.set_option("kernel", request.param[0])
     e.set_option("ept", request.param[1])
