@@ -38,6 +38,24 @@ def b_alg(nnz, rows, cols):
     return 12 * nnz + 4 * (rows + 1) + 8 * cols + 8 * rows
 
 
+KERNEL_NAMES = {0: "spmv_rowseq_kernel", 1: "spmv_merge_kernel", 2: "spmv_merge_tma_kernel", 3: "spmv_flag_kernel",
+                4: "spmv_flag_ring_kernel", 5: "spmv_flag_warp_kernel"}
+
+
+def recorded_traffic(workload, rows, cols, slabs, mode, world, flags):
+    """DRAM bytes per step of the dominant kernel (ncu dram__bytes_read.sum + dram__bytes_write.sum, summed over
+    the kernel's launches of one step) from the committed capture of exactly this configuration, else None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if world != 1 or not os.path.exists(p):
+        return None, None
+    with open(p) as f:
+        for rec in json.load(f):
+            if (rec["workload"], rec["rows"], rec["cols"], rec["slabs"], rec["mode"], rec["flags"]) == \
+                    (workload, rows, cols, slabs, mode, flags):
+                return rec["dram_bytes_per_step"], rec["source"]
+    return None, None
+
+
 def measured_peak_gbs():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -187,6 +205,8 @@ def run_ours(args):
         eng.set_option("ept", args.ept)
     if args.ctas:
         eng.set_option("ctas_per_sm", args.ctas)
+    if args.ablate:
+        eng.set_option("ablate", args.ablate)
     t0 = time.perf_counter()
     eng.setup_synthetic(kind, rows, cols, npr, SEED, b2.F64)
     setup_s = time.perf_counter() - t0
@@ -232,6 +252,8 @@ def run_ours(args):
     k_ns, k_n = eng.stat("merge_kernel_ns"), eng.stat("merge_kernel_launches")
     eng.set_option("profile", 0)
     slabs = eng.stat("slabs")
+    eng_mode = eng.stat("mode")
+    traffic, traffic_src = recorded_traffic(args.workload, rows, cols, slabs, eng_mode, world, flags)
     kernel_ms_per_step = k_ns * 1e-6 / max(1, k_n) * slabs
     peak, peak_src = measured_peak_gbs()
     alg_local = 12 * lnnz + 4 * (lrows + 1) + 8 * cols + 8 * lrows
@@ -269,8 +291,10 @@ def run_ours(args):
                        "slabs": slabs, "persist_window": not args.no_persist, "setup_s": round(setup_s, 2)},
             "gb_s_algorithmic": b_alg(nnz, rows, cols) * args.steps / t_dev / 1e9 if world == 1 else None,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "spmv_merge_kernel", "kernel_ms_per_step": kernel_ms_per_step,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
+                         "kernel": KERNEL_NAMES.get(eng_mode, "?"), "kernel_ms_per_step": kernel_ms_per_step,
+                         "kernel_launches_per_step": slabs,
                          "algorithmic_bytes_per_step": alg_local, "frac_of_8TBs_nominal": achieved / 8000.0},
             "e2e": {"value": nnz * e2e_steps / t_e2e / 1e9, "unit": "GNNZ/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": 1e3 * t_e2e / e2e_steps},
@@ -298,6 +322,7 @@ def main():
     ap.add_argument("--ept", type=int, default=0, help="entries per thread of kernel 3 (8 or 16)")
     ap.add_argument("--kernel", type=int, default=0,
                     help="1 merge-path LDG-staged, 2 merge-path TMA-staged, 3 flagged, 4 flagged persistent TMA ring (default)")
+    ap.add_argument("--ablate", type=int, default=0, help="kernel 5 ablation level (measurement only; results are wrong)")
     ap.add_argument("--ctas", type=int, default=0, help="persistent CTAs per SM of kernel 4")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
     ap.add_argument("--no-persist", action="store_true")

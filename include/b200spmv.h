@@ -65,7 +65,10 @@ B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx ma
 
 /* Tunables, set before setup: "slabs" (column slabs, 0 = auto), "persist_bytes"
  * (L2 set-aside cap, 0 = device max), "require_aligned" (1 = enforce the 64-byte rule),
- * "keep_csc" (1 = keep the device CSC copy for b200spmv_get_csc), "profile". */
+ * "keep_csc" (1 = keep the device CSC copy for b200spmv_get_csc), "profile", "kernel" (1..5, see
+ * DESIGN.md 3.2; default 3), "ept", "ctas_per_sm" (kernel tuning), "world" then "rank" (take the
+ * place of rank r of w in the nnz-balanced row-block split WITHOUT a communicator: a single SpMV
+ * needs no collective; b200spmv_power_iterate does and refuses). */
 B200SPMV_API int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t value);
 
 /* ---- setup: upload CSC, transpose to CSR on the device (once, amortised) ------------- */

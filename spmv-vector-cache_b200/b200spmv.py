@@ -182,6 +182,18 @@ class Engine:
         return out.value
 
 
+def row_splits(rowptr, world):
+    """Host statement of the nnz-balanced row-block split (csrc/multi.cu splits_kernel):
+    split k = first row whose prefix of stored entries reaches k*nnz/world.  rowptr: CSR row pointer."""
+    rowptr = np.asarray(rowptr, dtype=np.uint64)
+    rows, nnz = rowptr.size - 1, int(rowptr[-1])
+    out = [0]
+    for k in range(1, world):
+        out.append(int(np.searchsorted(rowptr[:rows], np.uint64(nnz * k // world), side="left")))
+    out.append(rows)
+    return out
+
+
 def comm_unique_id():
     buf = C.create_string_buffer(128)
     rc = lib().b200spmv_comm_unique_id(buf)

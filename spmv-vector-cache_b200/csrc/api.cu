@@ -91,7 +91,15 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "keep_csc") ctx->opt_keep_csc = (int)value;
     else if (k == "ept") { if (value != 8 && value != 16) return b2_fail(ctx, B200SPMV_EINVAL, "ept must be 8 or 16"); ctx->opt_ept = (int)value; }
     else if (k == "kernel") { if (value < 1 || value > 5) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 1..5"); ctx->opt_kernel = (int)value; }
+    else if (k == "ablate") ctx->opt_ablate = (int)value;
     else if (k == "ctas_per_sm") { if (value < 1 || value > 8) return b2_fail(ctx, B200SPMV_EINVAL, "ctas_per_sm must be 1..8"); ctx->opt_ctas_per_sm = (int)value; }
+    else if (k == "world" || k == "rank") {
+        // row-block sharding without a communicator: a single SpMV needs no collective, so a
+        // rank can be given its place by hand (tests: all ranks of a split, one after the other, on one GPU)
+        if (ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "set rank / world before setup");
+        if (k == "world") { if (value < 1 || value > 64) return b2_fail(ctx, B200SPMV_EINVAL, "world must be 1..64"); ctx->world = (int)value; if (ctx->rank >= ctx->world) ctx->rank = 0; }
+        else { if (value < 0 || value >= ctx->world) return b2_fail(ctx, B200SPMV_EINVAL, "rank must be 0..world-1"); ctx->rank = (int)value; }
+    }
     else if (k == "profile") { ctx->opt_profile = (int)value; ctx->merge_kernel_ns = 0; ctx->merge_kernel_launches = 0; ctx->prof_n = 0; }
     else return b2_fail(ctx, B200SPMV_EINVAL, "unknown option");
     return 0;

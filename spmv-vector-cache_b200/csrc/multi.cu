@@ -261,6 +261,7 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
     if (!ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "power_iterate before setup");
     if (ctx->rows != ctx->cols) return b2_fail(ctx, B200SPMV_EINVAL, "power iteration needs a square matrix");
     if (ctx->world > 1 && !ctx->h_row_splits) return b2_fail(ctx, B200SPMV_ESTATE, "no row splits");
+    if (ctx->world > 1 && !ctx->comm) return b2_fail(ctx, B200SPMV_ESTATE, "iterated SpMV over several ranks needs b200spmv_comm_init");
     B2_CHECK(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
     const int is_u64 = ctx->dtype == B200SPMV_U64;

@@ -699,8 +699,10 @@ spmv_flag_ring_kernel(const uint32_t *__restrict__ colind, const uint64_t *__res
 constexpr int WK_ENTRIES = 256;  // per warp: 32 lanes x 8 entries
 constexpr int WK_PER_TILE = (int)(B2_FLAG_TILE / WK_ENTRIES);
 
-template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, int OCC>
-__global__ void __launch_bounds__(256, OCC)
+// ABL (measurement only, option "ablate"): 0 = the kernel; 1 = results kept in registers, no y / carry
+// stores; 2 = also no segmented scan; 3 = no row logic at all (streams + gathers + multiply-add)
+template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, int ABL>
+__global__ void __launch_bounds__(256, 4)
 spmv_flag_warp_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
                       const uint64_t *__restrict__ x, uint64_t *__restrict__ y,
                       const uint32_t *__restrict__ seg_row, uint32_t rows, const uint32_t *__restrict__ warp_seg,
@@ -723,6 +725,13 @@ spmv_flag_warp_kernel(const uint32_t *__restrict__ colind, const uint64_t *__res
 #pragma unroll
     for (int i = 0; i < EPT; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
 
+    if (ABL == 3) {
+        uint64_t a = 0;
+#pragma unroll
+        for (int i = 0; i < EPT; i++) a = Semi<DT>::add(a, Semi<DT>::mul(p[i], xv[i]));
+        if (a == 0x123456789abcdefull) y[0] = a + wbase;
+        return;
+    }
     uint32_t f = 0;
 #pragma unroll
     for (int i = 0; i < EPT; i++) f |= (c[i] >> 31) << i;
@@ -762,13 +771,23 @@ spmv_flag_warp_kernel(const uint32_t *__restrict__ colind, const uint64_t *__res
     const uint32_t below = bal & ((2u << lane) - 1u);
     const int start = below ? 31 - __clz(below) : 0;
     uint64_t S = acc;
+    uint64_t carry_in = 0;
+    if (ABL < 2) {
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
-        if (lane - d >= start) S = Semi<DT>::add(n, S);
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
+            if (lane - d >= start) S = Semi<DT>::add(n, S);
+        }
+        carry_in = __shfl_up_sync(0xffffffffu, S, 1);
+        if (lane == 0) carry_in = 0;
     }
-    uint64_t carry_in = __shfl_up_sync(0xffffffffu, S, 1);
-    if (lane == 0) carry_in = 0;
+    if (ABL >= 1) {
+        uint64_t a = Semi<DT>::add(Semi<DT>::add(S, carry_in), Semi<DT>::add(head, y_old));
+#pragma unroll
+        for (int i = 0; i < EPT; i++) a ^= p[i];
+        if (a == 0x123456789abcdefull) y[close_row & 1023] = a + start;
+        return;
+    }
 
     if (nfl != 0) {
         if (close_row != NO_ROW) {
@@ -1049,12 +1068,14 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
     } while (0)
 #define B2_LAUNCH_WARP(P, R, E)                                                                                     \
     do {                                                                                                           \
-        if (ctx->opt_ctas_per_sm == 5)                                                                             \
-            spmv_flag_warp_kernel<DT, P, R, E, 5><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
-        else if (ctx->opt_ctas_per_sm == 6)                                                                        \
-            spmv_flag_warp_kernel<DT, P, R, E, 6><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
+        if (ctx->opt_ablate == 1)                                                                                  \
+            spmv_flag_warp_kernel<DT, P, R, E, 1><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
+        else if (ctx->opt_ablate == 2)                                                                             \
+            spmv_flag_warp_kernel<DT, P, R, E, 2><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
+        else if (ctx->opt_ablate == 3)                                                                             \
+            spmv_flag_warp_kernel<DT, P, R, E, 3><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
         else                                                                                                       \
-            spmv_flag_warp_kernel<DT, P, R, E, 4><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
+            spmv_flag_warp_kernel<DT, P, R, E, 0><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
     } while (0)
             const uint32_t nw = nt * WK_PER_TILE;
             const uint32_t *wseg = m.warp_seg + (size_t)tb * WK_PER_TILE + sl;
