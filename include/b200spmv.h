@@ -139,6 +139,15 @@ B200SPMV_API int b200spmv_max_alive(b200spmv_ctx *ctx, uint32_t rows, uint32_t n
 B200SPMV_API int b200spmv_max_col_span(b200spmv_ctx *ctx, uint32_t cols, uint32_t nnz, const uint32_t *colptr,
                           const uint32_t *inds, uint32_t *out);
 
+/* ---- the vector cache as a model (chisel/cache-new/NoWMVectorCache.scala) ----------------------- */
+/* What the FPGA's direct-mapped write-back cache over y (2^depth_log2 one-element lines) would do on the
+ * CSC row-index stream `inds` (storage order): the counters software/HardwareSpMVNewCache.cpp:189-204
+ * reports.  cms != 0: bit 31 of an index is the row-start mark of SparseMatrix::markRowStarts and such a
+ * first touch does not read DRAM (cold-miss skip).
+ * out[7] = reads, readMisses, conflictEvictions, coldMissSkips, ddrReads, flushWrites, hits. */
+B200SPMV_API int b200spmv_vector_cache_model(b200spmv_ctx *ctx, uint32_t nnz, const uint32_t *inds, int depth_log2,
+                                int cms, uint64_t *out);
+
 #ifdef __cplusplus
 }
 #endif

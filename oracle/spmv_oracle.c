@@ -273,3 +273,32 @@ ORACLE_API void oracle_power_iterate_u64(uint32_t n, const uint32_t *colptr,
         memcpy(x, y, (size_t)n * 8);
     }
 }
+
+/* ------------------------------------------------------------------------- */
+/* Functional model of the direct-mapped write-back vector cache over y,      */
+/* chisel/cache-new/NoWMVectorCache.scala: index/tag split :14-24, hit/miss   */
+/* :94-95, fill (all invalid) :197-206, miss handling with eviction of a      */
+/* valid line :254-268, cold-miss skip on the row-start bit :240-252, flush   */
+/* of the valid lines :208-231.  Sequential, one access after the other.      */
+/* out[7]: reads, readMisses, conflictEvictions, coldMissSkips, ddrReads,     */
+/* flushWrites, hits.                                                         */
+/* ------------------------------------------------------------------------- */
+ORACLE_API void oracle_vector_cache_model(uint32_t nnz, const uint32_t *inds, int depth_log2, int cms, uint64_t *out)
+{
+    const uint32_t depth = 1u << depth_log2, set_mask = depth - 1u;
+    const uint32_t addr_mask = cms ? 0x7FFFFFFFu : 0xFFFFFFFFu;
+    uint32_t *tag = (uint32_t *)malloc((size_t)depth * sizeof(uint32_t));
+    unsigned char *valid = (unsigned char *)calloc(depth, 1);
+    uint64_t miss = 0, conflict = 0, cold = 0, flush = 0;
+    for (uint32_t e = 0; e < nnz; e++) {
+        const uint32_t a = inds[e] & addr_mask, set = a & set_mask, t = a >> depth_log2;
+        if (valid[set] && tag[set] == t) continue;              /* readHit */
+        miss++;                                                  /* regReadMissCount */
+        if (valid[set]) conflict++;                              /* needEvict: memWrReq */
+        if (cms && (inds[e] >> 31)) cold++;                      /* sColdMiss: no DDR read */
+        valid[set] = 1; tag[set] = t;                            /* sReadMiss3 */
+    }
+    for (uint32_t i = 0; i < depth; i++) flush += valid[i];      /* sFlush */
+    out[0] = nnz; out[1] = miss; out[2] = conflict; out[3] = cold; out[4] = miss - cold; out[5] = flush; out[6] = nnz - miss;
+    free(tag); free(valid);
+}

@@ -21,7 +21,7 @@ EXPORTS = [
     "b200spmv_set_x", "b200spmv_set_y", "b200spmv_fill_x_synthetic", "b200spmv_fill_y_zero",
     "b200spmv_get_x", "b200spmv_get_y", "b200spmv_get_csr", "b200spmv_get_csc", "b200spmv_stat_u64",
     "b200spmv_comm_unique_id", "b200spmv_comm_init", "b200spmv_power_iterate",
-    "b200spmv_mark_row_starts", "b200spmv_max_alive", "b200spmv_max_col_span",
+    "b200spmv_mark_row_starts", "b200spmv_max_alive", "b200spmv_max_col_span", "b200spmv_vector_cache_model",
 ]
 
 _lib = None
@@ -174,6 +174,14 @@ class Engine:
         self._ck(self.L.b200spmv_max_alive(self.ctx, C.c_uint32(rows), C.c_uint32(int(inds.size)), _p(inds),
                                            C.byref(out)), "max_alive")
         return out.value
+
+    def vector_cache_model(self, inds, depth_log2, cms):
+        """-> dict of the NewCache counters for the row-index stream `inds` (uint32, storage order)."""
+        out = np.zeros(7, dtype=np.uint64)
+        self._ck(self.L.b200spmv_vector_cache_model(self.ctx, C.c_uint32(inds.size), _p(inds), C.c_int(depth_log2),
+                                                    C.c_int(int(cms)), _p(out)), "vector_cache_model")
+        keys = ("reads", "readMisses", "conflictEvictions", "coldMissSkips", "ddrReads", "flushWrites", "hits")
+        return dict(zip(keys, (int(v) for v in out)))
 
     def max_col_span(self, cols, colptr, inds):
         out = C.c_uint32()
