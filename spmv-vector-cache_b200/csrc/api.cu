@@ -26,6 +26,7 @@ static void release_matrix(b200spmv_ctx *ctx)
     { uint64_t *v = (uint64_t *)ctx->csc_vals; b2_free(v); ctx->csc_vals = nullptr; }
     { uint64_t *v = (uint64_t *)ctx->d_x; b2_free(v); ctx->d_x = nullptr; }
     { uint64_t *v = (uint64_t *)ctx->d_y; b2_free(v); ctx->d_y = nullptr; }
+    { uint64_t *v = (uint64_t *)ctx->d_yin; b2_free(v); ctx->d_yin = nullptr; }
     ctx->ready = false;
 }
 
@@ -72,6 +73,7 @@ extern "C" void b200spmv_destroy(b200spmv_ctx *ctx)
     if (ctx->d_norm) cudaFree(ctx->d_norm);
     free(ctx->h_row_splits);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    if (ctx->ev_yin) cudaEventDestroy(ctx->ev_yin);
     cudaStreamDestroy(ctx->stream); cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
 }
@@ -132,8 +134,9 @@ static int csc_to_csr(b200spmv_ctx *ctx, uint32_t index_mask)
     for (int sl = 0; sl < ctx->slabs; sl++) {
         const uint32_t c0 = (uint32_t)std::min<uint64_t>((uint64_t)sl * ctx->slab_cols, ctx->cols);
         const uint32_t c1 = (uint32_t)std::min<uint64_t>((uint64_t)c0 + ctx->slab_cols, ctx->cols);
-        B2_CHECK(ctx, cudaMemcpy(&e0[sl], ctx->csc_colptr + c0, 4, cudaMemcpyDeviceToHost));
-        B2_CHECK(ctx, cudaMemcpy(&e1[sl], ctx->csc_colptr + c1, 4, cudaMemcpyDeviceToHost));
+        B2_CHECK(ctx, cudaMemcpyAsync(&e0[sl], ctx->csc_colptr + c0, 4, cudaMemcpyDeviceToHost, s));
+        B2_CHECK(ctx, cudaMemcpyAsync(&e1[sl], ctx->csc_colptr + c1, 4, cudaMemcpyDeviceToHost, s));
+        B2_CHECK(ctx, cudaStreamSynchronize(s));
         ctx->h_slab_off[sl] = off;
         ctx->h_slab_nnz[sl] = e1[sl] - e0[sl];
         off += ((uint64_t)(e1[sl] - e0[sl]) + B2_FLAG_TILE) / B2_FLAG_TILE * B2_FLAG_TILE;
@@ -227,6 +230,14 @@ extern "C" int b200spmv_setup_synthetic(b200spmv_ctx *ctx, int kind, uint32_t ro
 
 // ---- exec -----------------------------------------------------------------------------------
 
+// y[i] = yin[i] (+) y[i]
+template <int DT>
+__global__ void vec_accumulate_kernel(uint64_t *__restrict__ y, const uint64_t *__restrict__ yin, uint64_t n)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) y[i] = Semi<DT>::add(yin[i], y[i]);
+}
+
 extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host, int flags)
 {
     if (!ctx) return B200SPMV_EINVAL;
@@ -240,10 +251,31 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
     uint64_t *yh = (uint64_t *)y_host + ctx->row_begin;
     uint64_t *yd = (uint64_t *)ctx->d_y + ctx->row_begin;
     B2_CHECK(ctx, cudaMemcpyAsync(ctx->d_x, x_host, (size_t)ctx->cols * 8, cudaMemcpyHostToDevice, s));
-    if (flags & B200SPMV_ACCUMULATE)
+    // Accumulating with the throughput kernels: the upload of the caller's y rides on the copy stream while
+    // t = A*x is computed, then y = y_in + t (one more re-association of a sum those kernels re-associate
+    // anyway).  Strict order keeps the reference's sequence ((y_in + p1) + p2) ... and uploads y first.
+    const bool overlap_y = (flags & B200SPMV_ACCUMULATE) && !(flags & B200SPMV_STRICT_ORDER) && ctx->local_rows > 0 &&
+                           ctx->local_rows * 8ull >= (1ull << 20);
+    if (overlap_y) {
+        if (!ctx->d_yin) { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->rows)); ctx->d_yin = v; }
+        if (!ctx->ev_yin) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_yin, cudaEventDisableTiming));
+        B2_CHECK(ctx, cudaMemcpyAsync((uint64_t *)ctx->d_yin + ctx->row_begin, yh, (size_t)ctx->local_rows * 8,
+                                      cudaMemcpyHostToDevice, ctx->copy_stream));
+        B2_CHECK(ctx, cudaEventRecord(ctx->ev_yin, ctx->copy_stream));
+    } else if (flags & B200SPMV_ACCUMULATE) {
         B2_CHECK(ctx, cudaMemcpyAsync(yd, yh, (size_t)ctx->local_rows * 8, cudaMemcpyHostToDevice, s));
+    }
     B2_CHECK(ctx, cudaEventRecord(ctx->ev0, s));
-    B2_TRY(b2_spmv_launch(ctx, flags, s));
+    B2_TRY(b2_spmv_launch(ctx, overlap_y ? (flags & ~B200SPMV_ACCUMULATE) : flags, s));
+    if (overlap_y) {
+        B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_yin, 0));
+        const unsigned grid = (unsigned)std::min<uint64_t>(b2_div_up(ctx->local_rows, 256), (uint64_t)ctx->sms * 16);
+        const uint64_t *yin = (const uint64_t *)ctx->d_yin + ctx->row_begin;
+        if (ctx->dtype == B200SPMV_F64) vec_accumulate_kernel<B200SPMV_F64><<<grid, 256, 0, s>>>(yd, yin, ctx->local_rows);
+        else vec_accumulate_kernel<B200SPMV_U64><<<grid, 256, 0, s>>>(yd, yin, ctx->local_rows);
+        B2_CHECK(ctx, cudaGetLastError());
+        ctx->launches += 1;
+    }
     B2_CHECK(ctx, cudaEventRecord(ctx->ev1, s));
     B2_CHECK(ctx, cudaMemcpyAsync(yh, yd, (size_t)ctx->local_rows * 8, cudaMemcpyDeviceToHost, s));
     B2_CHECK(ctx, cudaStreamSynchronize(s));
@@ -292,13 +324,15 @@ extern "C" int b200spmv_exec_device(b200spmv_ctx *ctx, int iters, int flags, flo
 extern "C" int b200spmv_set_x(b200spmv_ctx *ctx, const void *x_host)
 {
     B2_NEED_READY(ctx);
-    B2_CHECK(ctx, cudaMemcpy(ctx->d_x, x_host, (size_t)ctx->cols * 8, cudaMemcpyHostToDevice));
+    B2_CHECK(ctx, cudaMemcpyAsync(ctx->d_x, x_host, (size_t)ctx->cols * 8, cudaMemcpyHostToDevice, ctx->stream));
+    B2_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     return 0;
 }
 extern "C" int b200spmv_set_y(b200spmv_ctx *ctx, const void *y_host)
 {
     B2_NEED_READY(ctx);
-    B2_CHECK(ctx, cudaMemcpy(ctx->d_y, y_host, (size_t)ctx->rows * 8, cudaMemcpyHostToDevice));
+    B2_CHECK(ctx, cudaMemcpyAsync(ctx->d_y, y_host, (size_t)ctx->rows * 8, cudaMemcpyHostToDevice, ctx->stream));
+    B2_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     return 0;
 }
 extern "C" int b200spmv_fill_x_synthetic(b200spmv_ctx *ctx, uint64_t seed)
@@ -309,7 +343,8 @@ extern "C" int b200spmv_fill_x_synthetic(b200spmv_ctx *ctx, uint64_t seed)
 extern "C" int b200spmv_fill_y_zero(b200spmv_ctx *ctx)
 {
     B2_NEED_READY(ctx);
-    B2_CHECK(ctx, cudaMemset(ctx->d_y, 0, (size_t)ctx->rows * 8));
+    B2_CHECK(ctx, cudaMemsetAsync(ctx->d_y, 0, (size_t)ctx->rows * 8, ctx->stream));
+    B2_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     return 0;
 }
 extern "C" int b200spmv_get_x(b200spmv_ctx *ctx, void *x_host)

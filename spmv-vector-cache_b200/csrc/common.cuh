@@ -88,6 +88,8 @@ struct b200spmv_ctx {
     // vectors (device): x is the full replicated vector, y the full-length result (only
     // [row_begin,row_end) is written by this rank)
     void *d_x = nullptr, *d_y = nullptr;
+    void *d_yin = nullptr;        // the caller's y while t = A*x is computed (b200spmv_exec, accumulate)
+    cudaEvent_t ev_yin = nullptr;
     void *pin_x = nullptr, *pin_y = nullptr;  // pinned staging for pageable host vectors
     size_t pin_x_bytes = 0, pin_y_bytes = 0;
     bool persist_set = false;

@@ -220,7 +220,10 @@ int b2_shard_csc(b200spmv_ctx *ctx, uint32_t index_mask)
         flag_block_kernel<<<wide, 256, 0, s>>>(ctx->csc_rowind, index_mask, n, rb, re, flag);
         if ((rc = b2_exclusive_scan_u32(ctx, flag, n + 1, s))) break;
         uint32_t ln = 0;
-        cudaMemcpy(&ln, flag + n, 4, cudaMemcpyDeviceToHost);
+        // ctx->stream is non-blocking: the legacy default stream does not wait for it
+        if (cudaMemcpyAsync(&ln, flag + n, 4, cudaMemcpyDeviceToHost, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess) {
+            rc = b2_fail(ctx, B200SPMV_ECUDA, "block size copy failed"); break;
+        }
         if ((rc = b2_alloc(ctx, &new_row, ln))) break;
         if ((rc = b2_alloc(ctx, &new_val, ln))) break;
         if ((rc = b2_alloc(ctx, &new_colptr, (size_t)cols + 1))) break;

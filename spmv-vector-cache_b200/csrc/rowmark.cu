@@ -90,9 +90,9 @@ extern "C" int b200spmv_mark_row_starts(b200spmv_ctx *ctx, uint32_t rows, uint32
     uint32_t *d = nullptr;
     B2_TRY(b2_alloc(ctx, &d, nnz));
     int rc = 0;
-    if (cudaMemcpy(d, inds, (size_t)nnz * 4, cudaMemcpyHostToDevice) != cudaSuccess) rc = b2_fail(ctx, B200SPMV_ECUDA, "H2D failed");
+    if (cudaMemcpyAsync(d, inds, (size_t)nnz * 4, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) rc = b2_fail(ctx, B200SPMV_ECUDA, "H2D failed");
     if (!rc) rc = mark_on_device(ctx, rows, nnz, d, reverse, shift, ctx->stream);
-    if (!rc && cudaMemcpy(inds, d, (size_t)nnz * 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = b2_fail(ctx, B200SPMV_ECUDA, "D2H failed");
+    if (!rc && (cudaMemcpyAsync(inds, d, (size_t)nnz * 4, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)) rc = b2_fail(ctx, B200SPMV_ECUDA, "D2H failed");
     cudaFree(d);
     return rc;
 }
@@ -110,7 +110,7 @@ extern "C" int b200spmv_max_alive(b200spmv_ctx *ctx, uint32_t rows, uint32_t nnz
         if ((rc = b2_alloc(ctx, &d, nnz))) break;
         if ((rc = b2_alloc(ctx, &delta, nnz))) break;
         if ((rc = b2_alloc(ctx, &d_out, 1))) break;
-        if (cudaMemcpy(d, inds, (size_t)nnz * 4, cudaMemcpyHostToDevice) != cudaSuccess) { rc = b2_fail(ctx, B200SPMV_ECUDA, "H2D failed"); break; }
+        if (cudaMemcpyAsync(d, inds, (size_t)nnz * 4, cudaMemcpyHostToDevice, s) != cudaSuccess) { rc = b2_fail(ctx, B200SPMV_ECUDA, "H2D failed"); break; }
         if ((rc = mark_on_device(ctx, rows, nnz, d, 0, 31, s))) break;
         if ((rc = mark_on_device(ctx, rows, nnz, d, 1, 30, s))) break;
         const unsigned grid = (unsigned)std::min<uint64_t>(b2_div_up(nnz, 256), (uint64_t)ctx->sms * 32);

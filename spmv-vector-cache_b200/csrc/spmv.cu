@@ -907,8 +907,9 @@ int b2_build_tiles(b200spmv_ctx *ctx)
     uint32_t total = 0;
     for (int s = 0; s < ctx->slabs; s++) {
         uint32_t b = 0, e = 0;
-        B2_CHECK(ctx, cudaMemcpy(&b, m.rowptr + s * stride, 4, cudaMemcpyDeviceToHost));
-        B2_CHECK(ctx, cudaMemcpy(&e, m.rowptr + s * stride + ctx->local_rows, 4, cudaMemcpyDeviceToHost));
+        B2_CHECK(ctx, cudaMemcpyAsync(&b, m.rowptr + s * stride, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        B2_CHECK(ctx, cudaMemcpyAsync(&e, m.rowptr + s * stride + ctx->local_rows, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        B2_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
         const uint64_t items = (uint64_t)ctx->local_rows + (e - b);
         ctx->h_tile_base[s] = total;
         total += b2_div_up(items, MP_TILE);

@@ -150,8 +150,9 @@ int b2_synth_build_csc(b200spmv_ctx *ctx, int kind, uint32_t npr, uint64_t seed)
         const uint32_t rb = splits[ctx->rank], re = splits[ctx->rank + 1];
         ctx->row_begin = rb; ctx->row_end = re; ctx->local_rows = re - rb;
         uint32_t pb = 0, pe = 0;
-        cudaMemcpy(&pb, rowptr + rb, 4, cudaMemcpyDeviceToHost);
-        cudaMemcpy(&pe, rowptr + re, 4, cudaMemcpyDeviceToHost);
+        cudaMemcpyAsync(&pb, rowptr + rb, 4, cudaMemcpyDeviceToHost, s);
+        cudaMemcpyAsync(&pe, rowptr + re, 4, cudaMemcpyDeviceToHost, s);
+        if (cudaStreamSynchronize(s) != cudaSuccess) { rc = b2_fail(ctx, B200SPMV_ECUDA, "row block copy failed"); break; }
         const uint64_t ln = pe - pb;
         ctx->local_nnz = ln;
 

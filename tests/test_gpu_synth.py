@@ -135,3 +135,28 @@ def test_power_iteration_single_gpu(b2, oracle, dtype):
         assert np.allclose(x_gpu, x, rtol=1e-11, atol=1e-15)
     assert ms > 0
     e.close()
+
+
+@pytest.mark.parametrize("dtype", ["u64", "f64"])
+def test_exec_accumulates_onto_a_nonzero_host_y(b2, dtype):
+    """b200spmv_exec with ACCUMULATE on vectors large enough (>= 1 MB) for the overlapped upload of y:
+    y_out = y_in + A*x.  u64: bit-equal to the strict kernel; f64: y_in + t within one rounding of it."""
+    rows = 1 << 18
+    e = b2.Engine(0)
+    e.setup_synthetic(0, rows, rows, 16, SEED, DT(b2, dtype))
+    e.fill_x_synthetic(SEED + 1)
+    x = e.get_x()
+    npdt = np.uint64 if dtype == "u64" else np.float64
+    y_in = H.make_x(rows, dtype, "rand", 77)
+    y_strict = y_in.copy()
+    e.exec(x, y_strict, b2.ACCUMULATE | b2.STRICT_ORDER)
+    y = y_in.copy()
+    e.exec(x, y, b2.ACCUMULATE)
+    if dtype == "u64":
+        assert y.tobytes() == y_strict.tobytes()
+    else:
+        t = np.zeros(rows, dtype=npdt)
+        e.exec(x, t, 0)
+        assert (y == y_in + t).all()
+        assert np.allclose(y, y_strict, rtol=0, atol=2 * 17 * EPS * (np.abs(y_in).max() + 16.0))
+    e.close()
