@@ -197,6 +197,12 @@ def run_ours(args):
             uid.copy_(torch.frombuffer(bytearray(b2.comm_unique_id()), dtype=torch.uint8))
         dist.broadcast(uid, 0)
         eng.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
+    if args.shard:  # one rank's row block of a W-way split, alone on this GPU (tuning runs; no collective)
+        r_, w_ = (int(v) for v in args.shard.split("/"))
+        eng.set_option("world", w_)
+        eng.set_option("rank", r_)
+    if args.dcsr is not None:
+        eng.set_option("dcsr_x16", args.dcsr)
     if args.slabs:
         eng.set_option("slabs", args.slabs)
     if args.kernel:
@@ -226,7 +232,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    power = args.workload == "banded-power"
+    power = args.workload == "banded-power" and not args.shard
     sampler = ClockSampler(local)
     # ---- device-resident timing: W warm-up, then exactly K steps --------------------------
     if power:
@@ -244,7 +250,7 @@ def run_ours(args):
     barrier()
     launches = eng.stat("launches") - launches0
     t_dev = max_over_ranks(ms_total) * 1e-3
-    value = nnz * args.steps / t_dev / 1e9
+    value = (lnnz if args.shard else nnz) * args.steps / t_dev / 1e9
 
     # ---- the dominant kernel alone (roofline), same workload, events around each launch ----
     eng.set_option("profile", 1)
@@ -317,6 +323,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="uniform", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the row count (experiments only)")
+    ap.add_argument("--shard", default="", help="R/W: run rank R's row block of a W-way split alone (experiments only)")
+    ap.add_argument("--dcsr", type=int, default=None, help="hypersparse-slab threshold x16 (0 = never use spmv_dcsr_kernel)")
     ap.add_argument("--cols", type=int, default=0, help="override the column count (experiments only)")
     ap.add_argument("--slabs", type=int, default=0)
     ap.add_argument("--ept", type=int, default=0, help="entries per thread of kernel 3 (8 or 16)")

@@ -823,6 +823,34 @@ spmv_flag_warp_kernel(const uint32_t *__restrict__ colind, const uint64_t *__res
     }
 }
 
+// ---- hypersparse slabs: one thread per NON-EMPTY row --------------------------------------------
+// A column slab of a matrix with far more columns than fit L2 (banded + random over 128M columns cut into
+// 18 slabs) holds well under two entries per non-empty row.  The flagged kernel then has a row-start flag
+// on almost every entry and falls into its per-flag path; here thread k simply owns the k-th non-empty row
+// (seg_row, built at setup), walks its one or two entries in storage order and read-modify-writes y.
+// All loads of neighbouring threads are neighbours (entries of consecutive non-empty rows are consecutive),
+// y is touched in ascending order.  Summation order is the reference's, so this path is bit-exact in fp64.
+// (A variant with four rows per thread and their loads issued together was slower: 2.30 vs 1.98 ms on the C5
+// shard -- neighbouring lanes no longer touch neighbouring entries.  profiles/r01_c5_shard_sweep.txt)
+template <int DT, bool PERSIST, bool READ_Y>
+__global__ void __launch_bounds__(256)
+spmv_dcsr_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
+                 const uint64_t *__restrict__ x, uint64_t *__restrict__ y, const uint32_t *__restrict__ seg_row,
+                 uint32_t nseg, uint32_t colmask)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nseg) return;
+    const uint32_t row = __ldg(seg_row + k);
+    const uint32_t b = __ldg(rowptr + row), e = __ldg(rowptr + row + 1);
+    uint64_t acc = READ_Y ? y[row] : 0ull;
+    const uint64_t pol_keep = policy_evict_last();
+    for (uint32_t p = b; p < e; p++) {
+        const uint32_t c = __ldg(colind + p) & colmask;
+        acc = Semi<DT>::add(acc, Semi<DT>::mul(__ldg(reinterpret_cast<const unsigned long long *>(vals + p)), load_x<PERSIST>(x, c, pol_keep)));
+    }
+    y[row] = acc;
+}
+
 // ---- setup of the flagged format (once per matrix) ---------------------------------------------
 __global__ void nonempty_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, uint32_t *__restrict__ ne)
 {
@@ -1047,6 +1075,22 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
             if (prof) {
                 if (!ctx->prof_ev[ctx->prof_n]) { cudaEventCreate(&ctx->prof_ev[ctx->prof_n]); cudaEventCreate(&ctx->prof_ev[ctx->prof_n + 1]); }
                 cudaEventRecord(ctx->prof_ev[ctx->prof_n], s);
+            }
+            // hypersparse slab (fewer than opt_dcsr_x16/16 entries per non-empty row): thread per non-empty row
+            const uint32_t nseg = ctx->h_nseg[sl];
+            if (ctx->opt_dcsr_x16 > 0 && nseg > 0 && (uint64_t)ctx->h_slab_nnz[sl] * 16 < (uint64_t)nseg * ctx->opt_dcsr_x16) {
+                const unsigned grid = b2_div_up(nseg, 256);
+                if (persist) {
+                    if (read_y) spmv_dcsr_kernel<DT, true, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+                    else spmv_dcsr_kernel<DT, true, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+                } else {
+                    if (read_y) spmv_dcsr_kernel<DT, false, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+                    else spmv_dcsr_kernel<DT, false, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+                }
+                if (prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
+                ctx->launches += 1;
+                B2_CHECK(ctx, cudaGetLastError());
+                continue;
             }
 #define B2_LAUNCH_FLAG(P, R, E)                                                                                     \
     do {                                                                                                           \

@@ -222,6 +222,11 @@ int main(int argc, char **argv)
     int sms = 0;
     CK(cudaSetDevice(0));
     CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    if (getenv("FETCH")) {  // L2 fetch granularity hint: 32, 64 or 128 bytes
+        CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(getenv("FETCH"))));
+        size_t g = 0; CK(cudaDeviceGetLimit(&g, cudaLimitMaxL2FetchGranularity));
+        printf("L2 fetch granularity limit = %zu\n", g);
+    }
     const uint64_t n = 1ull << 28;
     const uint32_t table = (uint32_t)(mb * 1048576 / 8);
     uint32_t *idx; uint64_t *tab, *out;
