@@ -294,7 +294,8 @@ def run_ours(args):
                        "partition": "nnz-balanced row blocks, no collective" if not power else
                                     "row blocks + x all-gather per step",
                        "l2": "inputs (%.1f GB) larger than L2; no flush" % (b_alg(nnz, rows, cols) / 1e9),
-                       "slabs": slabs, "persist_window": not args.no_persist, "setup_s": round(setup_s, 2)},
+                       "slabs": slabs, "persist_window": not args.no_persist, "setup_s": round(setup_s, 2),
+                       **({"x_exchange_ms_last_step": eng.stat("xchgtime_ns") * 1e-6} if power and world > 1 else {})},
             "gb_s_algorithmic": b_alg(nnz, rows, cols) * args.steps / t_dev / 1e9 if world == 1 else None,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,

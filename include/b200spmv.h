@@ -113,7 +113,7 @@ B200SPMV_API int b200spmv_get_csc(b200spmv_ctx *ctx, uint32_t *colptr, uint32_t 
 
 /* ---- statistics: SpMV::statInt / statKeys (software/SpMV.h:28-29) ---------------------- */
 /* keys: rows cols nz local_rows local_nz row_begin row_end spmvtime_ns xfertime_ns
- * setuptime_ns transposetime_ns slabs l2_persist_bytes l2_bytes sms gpus rank mode
+ * setuptime_ns transposetime_ns xchgtime_ns (x exchange of the last power-iteration step) slabs l2_persist_bytes l2_bytes sms gpus rank mode
  * launches cuda_error tiles; with option "profile"=1 also merge_kernel_ns and
  * merge_kernel_launches (CUDA-event time of the merge-path kernel alone, for the roofline) */
 B200SPMV_API int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *out);

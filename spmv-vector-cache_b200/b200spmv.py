@@ -199,6 +199,11 @@ def row_splits(rowptr, world):
     for k in range(1, world):
         out.append(int(np.searchsorted(rowptr[:rows], np.uint64(nnz * k // world), side="left")))
     out.append(rows)
+    if world > 1 and rows % world == 0:  # equal row counts when they are balanced to 2 % anyway (common.cuh b2_row_splits)
+        per = rows // world
+        worst = max(int(rowptr[(r + 1) * per] - rowptr[r * per]) for r in range(world))
+        if worst * 100 * world <= 102 * nnz + 100 * world:
+            return [r * per for r in range(world + 1)]
     return out
 
 

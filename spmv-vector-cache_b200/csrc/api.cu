@@ -74,6 +74,7 @@ extern "C" void b200spmv_destroy(b200spmv_ctx *ctx)
     free(ctx->h_row_splits);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     if (ctx->ev_yin) cudaEventDestroy(ctx->ev_yin);
+    if (ctx->ev_x0) { cudaEventDestroy(ctx->ev_x0); cudaEventDestroy(ctx->ev_x1); }
     cudaStreamDestroy(ctx->stream); cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
 }
@@ -419,6 +420,7 @@ extern "C" int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *o
     else if (k == "xfertime_ns") *out = ctx->xfertime_ns;
     else if (k == "setuptime_ns") *out = ctx->setuptime_ns;
     else if (k == "transposetime_ns") *out = ctx->transposetime_ns;
+    else if (k == "xchgtime_ns") *out = ctx->xchgtime_ns;
     else if (k == "slabs") *out = (uint64_t)ctx->slabs;
     else if (k == "l2_persist_bytes") *out = ctx->max_persist_bytes;
     else if (k == "l2_bytes") *out = ctx->l2_bytes;

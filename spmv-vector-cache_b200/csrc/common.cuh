@@ -91,6 +91,8 @@ struct b200spmv_ctx {
     void *d_x = nullptr, *d_y = nullptr;
     void *d_yin = nullptr;        // the caller's y while t = A*x is computed (b200spmv_exec, accumulate)
     cudaEvent_t ev_yin = nullptr;
+    cudaEvent_t ev_x0 = nullptr, ev_x1 = nullptr;  // around the x exchange of the last power-iteration step
+    uint64_t xchgtime_ns = 0;
     void *pin_x = nullptr, *pin_y = nullptr;  // pinned staging for pageable host vectors
     size_t pin_x_bytes = 0, pin_y_bytes = 0;
     bool persist_set = false;
@@ -232,6 +234,42 @@ __device__ __forceinline__ uint64_t ld_gather_u64(const void *p, uint64_t pol)
     uint64_t r;
     asm volatile("ld.global.nc.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(r) : "l"(p), "l"(pol));
     return r;
+}
+
+// Row-block split of `rows` rows over `world` ranks, one thread block of >= world+1 threads:
+// nnz-balanced -- split k = first row whose prefix of stored entries reaches k*nnz/world -- unless plain
+// equal row counts are already balanced to 2 % (banded and uniform matrices): equal blocks let the iterated
+// SpMV refresh x with one in-place ncclAllGather instead of a group of broadcasts.
+__device__ __forceinline__ void b2_row_splits(const uint32_t *__restrict__ rowptr, uint32_t rows, int world,
+                                              uint32_t *__restrict__ splits)
+{
+    const int k = threadIdx.x;
+    if (k <= world) {
+        uint32_t v;
+        if (k == 0) v = 0;
+        else if (k == world) v = rows;
+        else {
+            const uint64_t target = (uint64_t)rowptr[rows] * k / world;
+            uint32_t lo = 0, hi = rows;
+            while (lo < hi) {
+                const uint32_t mid = lo + ((hi - lo) >> 1);
+                if (rowptr[mid] < target) lo = mid + 1; else hi = mid;
+            }
+            v = lo;
+        }
+        splits[k] = v;
+    }
+    __syncthreads();
+    if (k == 0 && world > 1 && rows % (uint32_t)world == 0) {
+        const uint32_t per = rows / (uint32_t)world;
+        uint64_t worst = 0;
+        for (int r = 0; r < world; r++) {
+            const uint64_t n = (uint64_t)rowptr[(r + 1) * per] - rowptr[r * per];
+            worst = n > worst ? n : worst;
+        }
+        if (worst * 100ull * (uint64_t)world <= 102ull * (uint64_t)rowptr[rows] + 100ull * (uint64_t)world)
+            for (int r = 0; r <= world; r++) splits[r] = r * per;
+    }
 }
 
 // semiring (chisel/frontend/SemiringOp.scala): fp64 = separate IEEE multiply and add, never

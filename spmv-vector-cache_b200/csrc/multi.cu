@@ -20,6 +20,7 @@ typedef int (*fn_init_rank)(ncclComm **, int, nccl_uid, int);
 typedef int (*fn_destroy)(ncclComm *);
 typedef int (*fn_allreduce)(const void *, void *, size_t, int, int, ncclComm *, cudaStream_t);
 typedef int (*fn_bcast)(const void *, void *, size_t, int, int, ncclComm *, cudaStream_t);
+typedef int (*fn_allgather)(const void *, void *, size_t, int, ncclComm *, cudaStream_t);
 typedef int (*fn_group)(void);
 typedef const char *(*fn_errstr)(int);
 
@@ -30,6 +31,7 @@ struct NcclApi {
     fn_destroy destroy = nullptr;
     fn_allreduce allreduce = nullptr;
     fn_bcast bcast = nullptr;
+    fn_allgather allgather = nullptr;
     fn_group group_start = nullptr, group_end = nullptr;
     fn_errstr errstr = nullptr;
 } g_nccl;
@@ -49,6 +51,7 @@ bool load_nccl(std::string *why)
     g_nccl.destroy = (fn_destroy)dlsym(h, "ncclCommDestroy");
     g_nccl.allreduce = (fn_allreduce)dlsym(h, "ncclAllReduce");
     g_nccl.bcast = (fn_bcast)dlsym(h, "ncclBroadcast");
+    g_nccl.allgather = (fn_allgather)dlsym(h, "ncclAllGather");
     g_nccl.group_start = (fn_group)dlsym(h, "ncclGroupStart");
     g_nccl.group_end = (fn_group)dlsym(h, "ncclGroupEnd");
     g_nccl.errstr = (fn_errstr)dlsym(h, "ncclGetErrorString");
@@ -76,17 +79,7 @@ __global__ void row_hist_kernel(const uint32_t *__restrict__ rowind, uint32_t ma
 }
 __global__ void splits_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, int world, uint32_t *__restrict__ splits)
 {
-    const int k = threadIdx.x;
-    if (k > world) return;
-    if (k == 0) { splits[0] = 0; return; }
-    if (k == world) { splits[k] = rows; return; }
-    const uint64_t target = (uint64_t)rowptr[rows] * k / world;
-    uint32_t lo = 0, hi = rows;
-    while (lo < hi) {
-        const uint32_t mid = lo + ((hi - lo) >> 1);
-        if (rowptr[mid] < target) lo = mid + 1; else hi = mid;
-    }
-    splits[k] = lo;
+    b2_row_splits(rowptr, rows, world, splits);
 }
 __global__ void flag_block_kernel(const uint32_t *__restrict__ rowind, uint32_t mask, uint64_t n, uint32_t rb,
                                   uint32_t re, uint32_t *__restrict__ flag)
@@ -248,6 +241,14 @@ static int allgather_x(b200spmv_ctx *ctx, cudaStream_t s)
 {
     if (ctx->world == 1) return 0;
     uint64_t *x = (uint64_t *)ctx->d_x;
+    // equal blocks (b2_row_splits prefers them when they are balanced): one in-place all-gather
+    bool equal = g_nccl.allgather != nullptr;
+    const uint32_t per = ctx->h_row_splits[1] - ctx->h_row_splits[0];
+    for (int r = 0; r < ctx->world && equal; r++) equal = ctx->h_row_splits[r + 1] - ctx->h_row_splits[r] == per;
+    if (equal) {
+        NCCL_TRY(ctx, g_nccl.allgather(x + (size_t)ctx->rank * per, x, (size_t)per, NCCL_UINT64, ctx->comm, s));
+        return 0;
+    }
     NCCL_TRY(ctx, g_nccl.group_start());
     for (int r = 0; r < ctx->world; r++) {
         const uint32_t b = ctx->h_row_splits[r], e = ctx->h_row_splits[r + 1];
@@ -289,13 +290,23 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
         }
         scale_into_x_kernel<<<ctx->sms * 8, 256, 0, s>>>(yb, ctx->local_rows, norm2, is_u64, xb);
         ctx->launches += is_u64 ? 1 : 3;
+        const bool timed = it == steps - 1 && ctx->world > 1;  // exchange time of the last step -> stat "xchgtime_ns"
+        if (timed) {
+            if (!ctx->ev_x0) { B2_CHECK(ctx, cudaEventCreate(&ctx->ev_x0)); B2_CHECK(ctx, cudaEventCreate(&ctx->ev_x1)); }
+            B2_CHECK(ctx, cudaEventRecord(ctx->ev_x0, s));
+        }
         B2_TRY(allgather_x(ctx, s));
+        if (timed) B2_CHECK(ctx, cudaEventRecord(ctx->ev_x1, s));
     }
     B2_CHECK(ctx, cudaEventRecord(ctx->ev1, s));
     B2_CHECK(ctx, cudaStreamSynchronize(s));
     float ms = 0.f;
     B2_CHECK(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
     if (ms_total) *ms_total = ms;
+    if (ctx->world > 1 && ctx->ev_x0) {
+        float mx = 0.f;
+        if (cudaEventElapsedTime(&mx, ctx->ev_x0, ctx->ev_x1) == cudaSuccess) ctx->xchgtime_ns = (uint64_t)((double)mx * 1e6);
+    }
     if (last_norm) {
         double h = 0.0;
         if (!is_u64) B2_CHECK(ctx, cudaMemcpy(&h, norm2, 8, cudaMemcpyDeviceToHost));

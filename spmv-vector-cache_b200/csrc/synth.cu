@@ -27,20 +27,9 @@ __global__ void rmat_hist_kernel(uint64_t seed, int scale, uint64_t nedges, uint
 }
 
 // nnz-balanced row blocks: split k = first row whose prefix reaches k*nnz/world
-__global__ void find_splits_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, int world,
-                                   uint32_t *__restrict__ splits)
+__global__ void find_splits_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, int world, uint32_t *__restrict__ splits)
 {
-    const int k = threadIdx.x;
-    if (k > world) return;
-    if (k == 0) { splits[0] = 0; return; }
-    if (k == world) { splits[k] = rows; return; }
-    const uint64_t target = (uint64_t)rowptr[rows] * k / world;
-    uint32_t lo = 0, hi = rows;
-    while (lo < hi) {
-        const uint32_t mid = lo + ((hi - lo) >> 1);
-        if (rowptr[mid] < target) lo = mid + 1; else hi = mid;
-    }
-    splits[k] = lo;
+    b2_row_splits(rowptr, rows, world, splits);
 }
 
 __global__ void local_rowptr_kernel(const uint32_t *__restrict__ rowptr, uint32_t rb, uint32_t nlocal,
