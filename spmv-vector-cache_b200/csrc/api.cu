@@ -95,6 +95,7 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "ept") { if (value != 8 && value != 16) return b2_fail(ctx, B200SPMV_EINVAL, "ept must be 8 or 16"); ctx->opt_ept = (int)value; }
     else if (k == "kernel") { if (value < 1 || value > 5) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 1..5"); ctx->opt_kernel = (int)value; }
     else if (k == "dcsr_x16") ctx->opt_dcsr_x16 = (int)value;
+    else if (k == "prefetch_tiles") ctx->opt_prefetch_tiles = (int)std::max<int64_t>(0, value);
     else if (k == "ablate") ctx->opt_ablate = (int)value;
     else if (k == "ctas_per_sm") { if (value < 1 || value > 8) return b2_fail(ctx, B200SPMV_EINVAL, "ctas_per_sm must be 1..8"); ctx->opt_ctas_per_sm = (int)value; }
     else if (k == "world" || k == "rank") {
@@ -117,12 +118,12 @@ static int choose_slabs(const b200spmv_ctx *ctx)
     const double l2 = (double)ctx->l2_bytes;
     if (l2 <= 0 || xbytes <= 0.6 * l2) return 1;
     int s = std::min(64, (int)std::ceil(xbytes / (0.45 * l2)));
-    // Every slab after the first read-modify-writes y once more.  When the rows are so short that an
-    // L2-sized slab would hold only a few entries per row (C5: 16 entries per row over 18 slabs), that
-    // costs more than it saves: keep at least ~2 entries per row and slab and let part of the gathers
-    // go to HBM (profiles/r01_c5_shard_sweep.txt).
+    // Every slab after the first read-modify-writes y once more and shortens the row pieces the kernels
+    // work on.  When an L2-sized slab would hold only a few entries per row (C5: 16 entries per row over 18
+    // slabs; C4: 32 over 9) that costs more than the L2 hits save: keep >= 8 entries per row and slab and
+    // let part of the gathers go to HBM (profiles/r01_c5_shard_sweep.txt, r01_c4_shard_sweep.txt).
     const double per_row = ctx->local_rows ? (double)ctx->local_nnz / (double)ctx->local_rows : 0.0;
-    if (per_row / s < 4.0) s = std::max(1, std::min(s, (int)(per_row / 2.0)));
+    s = std::max(1, std::min(s, (int)(per_row / 8.0)));
     return s;
 }
 

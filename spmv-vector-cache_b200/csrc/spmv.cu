@@ -366,9 +366,18 @@ __global__ void __launch_bounds__(B2_FLAG_TILE / EPT, EPT == 8 ? 4 : 4)
 spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
                  const uint64_t *__restrict__ x, uint64_t *__restrict__ y,
                  const uint32_t *__restrict__ seg_row, uint32_t rows, const uint32_t *__restrict__ tile_seg,
-                 uint32_t *__restrict__ carry_row, uint64_t *__restrict__ carry_val)
+                 uint32_t *__restrict__ carry_row, uint64_t *__restrict__ carry_val, uint32_t pf_dist)
 {
     constexpr int THREADS = B2_FLAG_TILE / EPT, WARPS = THREADS / 32;
+    // one thread asks the TMA unit to pull the streams of the tile `pf_dist` CTAs ahead into L2 (two bulk
+    // prefetches, no registers, no data returned to the SM): that CTA then starts on L2 hits instead of HBM
+    if (pf_dist != 0 && threadIdx.x == 0) {
+        const uint64_t tp = (uint64_t)blockIdx.x + pf_dist;
+        if (tp < gridDim.x) {
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vals + tp * B2_FLAG_TILE), "r"(B2_FLAG_TILE * 8u) : "memory");
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(colind + tp * B2_FLAG_TILE), "r"(B2_FLAG_TILE * 4u) : "memory");
+        }
+    }
     __shared__ uint32_t s_wcnt[WARPS];
     __shared__ uint32_t s_wflag[WARPS];
     __shared__ uint64_t s_wsum[WARPS];
@@ -1095,9 +1104,9 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
 #define B2_LAUNCH_FLAG(P, R, E)                                                                                     \
     do {                                                                                                           \
         if (ctx->opt_ept == 16)                                                                                    \
-            spmv_flag_kernel<DT, P, R, E, 16><<<nt, B2_FLAG_TILE / 16, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval); \
+            spmv_flag_kernel<DT, P, R, E, 16><<<nt, B2_FLAG_TILE / 16, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval, (uint32_t)ctx->opt_prefetch_tiles); \
         else                                                                                                       \
-            spmv_flag_kernel<DT, P, R, E, 8><<<nt, B2_FLAG_TILE / 8, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval);  \
+            spmv_flag_kernel<DT, P, R, E, 8><<<nt, B2_FLAG_TILE / 8, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval, (uint32_t)ctx->opt_prefetch_tiles);  \
     } while (0)
 #define B2_LAUNCH_RING(P, R, E)                                                                                     \
     do {                                                                                                           \
