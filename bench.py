@@ -186,6 +186,8 @@ def run_ours(args):
     if args.rows:
         rows = args.rows
     cols = args.cols or rows
+    if args.npr:
+        npr = args.npr
     flags = 0 if args.overwrite else b2.ACCUMULATE
     if args.no_persist:
         flags |= b2.NO_PERSIST
@@ -326,6 +328,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="uniform", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the row count (experiments only)")
+    ap.add_argument("--npr", type=int, default=0, help="override entries per row (experiments only)")
     ap.add_argument("--shard", default="", help="R/W: run rank R's row block of a W-way split alone (experiments only)")
     ap.add_argument("--dcsr", type=int, default=None, help="hypersparse-slab threshold x16 (0 = never use spmv_dcsr_kernel)")
     ap.add_argument("--cols", type=int, default=0, help="override the column count (experiments only)")
