@@ -73,7 +73,8 @@ extern "C" void b200spmv_destroy(b200spmv_ctx *ctx)
     if (ctx->d_norm) cudaFree(ctx->d_norm);
     free(ctx->h_row_splits);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
-    if (ctx->ev_yin) cudaEventDestroy(ctx->ev_yin);
+    for (int i = 0; i < Y_CHUNKS; i++) if (ctx->ev_ychunk[i]) cudaEventDestroy(ctx->ev_ychunk[i]);
+    for (int i = 0; i < 64; i++) if (ctx->ev_slab[i]) cudaEventDestroy(ctx->ev_slab[i]);
     if (ctx->ev_x0) { cudaEventDestroy(ctx->ev_x0); cudaEventDestroy(ctx->ev_x1); }
     cudaStreamDestroy(ctx->stream); cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
@@ -260,7 +261,20 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
     const uint64_t t0 = now_ns();
     uint64_t *yh = (uint64_t *)y_host + ctx->row_begin;
     uint64_t *yd = (uint64_t *)ctx->d_y + ctx->row_begin;
-    B2_CHECK(ctx, cudaMemcpyAsync(ctx->d_x, x_host, (size_t)ctx->cols * 8, cudaMemcpyHostToDevice, s));
+    // x goes up slab slice by slab slice on the copy stream: the kernels of slab s only gather from slice s,
+    // so they start as soon as it has landed (b2_spmv_launch waits on ev_slab[s]) while the rest still uploads
+    const bool sliced_x = ctx->slabs > 1 && !(flags & B200SPMV_STRICT_ORDER) && (size_t)ctx->cols * 8 >= (8u << 20);
+    if (sliced_x) {
+        for (int sl = 0; sl < ctx->slabs; sl++) {
+            const size_t c0 = (size_t)sl * ctx->slab_cols, c1 = std::min<size_t>(ctx->cols, c0 + ctx->slab_cols);
+            if (!ctx->ev_slab[sl]) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_slab[sl], cudaEventDisableTiming));
+            B2_CHECK(ctx, cudaMemcpyAsync((uint64_t *)ctx->d_x + c0, (const uint64_t *)x_host + c0, (c1 - c0) * 8,
+                                          cudaMemcpyHostToDevice, ctx->copy_stream));
+            B2_CHECK(ctx, cudaEventRecord(ctx->ev_slab[sl], ctx->copy_stream));
+        }
+    } else {
+        B2_CHECK(ctx, cudaMemcpyAsync(ctx->d_x, x_host, (size_t)ctx->cols * 8, cudaMemcpyHostToDevice, s));
+    }
     // Accumulating with the throughput kernels: the upload of the caller's y rides on the copy stream while
     // t = A*x is computed, then y = y_in + t (one more re-association of a sum those kernels re-associate
     // anyway).  Strict order keeps the reference's sequence ((y_in + p1) + p2) ... and uploads y first.
@@ -268,26 +282,41 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
                            ctx->local_rows * 8ull >= (1ull << 20);
     if (overlap_y) {
         if (!ctx->d_yin) { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->rows)); ctx->d_yin = v; }
-        if (!ctx->ev_yin) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_yin, cudaEventDisableTiming));
-        B2_CHECK(ctx, cudaMemcpyAsync((uint64_t *)ctx->d_yin + ctx->row_begin, yh, (size_t)ctx->local_rows * 8,
-                                      cudaMemcpyHostToDevice, ctx->copy_stream));
-        B2_CHECK(ctx, cudaEventRecord(ctx->ev_yin, ctx->copy_stream));
+        // in Y_CHUNKS row chunks, each with its own event: chunk k is added and sent back (other PCIe
+        // direction) while the chunks after it are still on their way up
+        for (int k = 0; k < Y_CHUNKS; k++) {
+            const uint64_t r0 = (uint64_t)ctx->local_rows * k / Y_CHUNKS, r1 = (uint64_t)ctx->local_rows * (k + 1) / Y_CHUNKS;
+            if (!ctx->ev_ychunk[k]) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_ychunk[k], cudaEventDisableTiming));
+            if (r1 > r0)
+                B2_CHECK(ctx, cudaMemcpyAsync((uint64_t *)ctx->d_yin + ctx->row_begin + r0, yh + r0, (size_t)(r1 - r0) * 8,
+                                              cudaMemcpyHostToDevice, ctx->copy_stream));
+            B2_CHECK(ctx, cudaEventRecord(ctx->ev_ychunk[k], ctx->copy_stream));
+        }
     } else if (flags & B200SPMV_ACCUMULATE) {
         B2_CHECK(ctx, cudaMemcpyAsync(yd, yh, (size_t)ctx->local_rows * 8, cudaMemcpyHostToDevice, s));
     }
     B2_CHECK(ctx, cudaEventRecord(ctx->ev0, s));
-    B2_TRY(b2_spmv_launch(ctx, overlap_y ? (flags & ~B200SPMV_ACCUMULATE) : flags, s));
-    if (overlap_y) {
-        B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_yin, 0));
-        const unsigned grid = (unsigned)std::min<uint64_t>(b2_div_up(ctx->local_rows, 256), (uint64_t)ctx->sms * 16);
-        const uint64_t *yin = (const uint64_t *)ctx->d_yin + ctx->row_begin;
-        if (ctx->dtype == B200SPMV_F64) vec_accumulate_kernel<B200SPMV_F64><<<grid, 256, 0, s>>>(yd, yin, ctx->local_rows);
-        else vec_accumulate_kernel<B200SPMV_U64><<<grid, 256, 0, s>>>(yd, yin, ctx->local_rows);
-        B2_CHECK(ctx, cudaGetLastError());
-        ctx->launches += 1;
-    }
+    ctx->wait_slab_events = sliced_x;
+    const int rc_launch = b2_spmv_launch(ctx, overlap_y ? (flags & ~B200SPMV_ACCUMULATE) : flags, s);
+    ctx->wait_slab_events = false;
+    B2_TRY(rc_launch);
     B2_CHECK(ctx, cudaEventRecord(ctx->ev1, s));
-    B2_CHECK(ctx, cudaMemcpyAsync(yh, yd, (size_t)ctx->local_rows * 8, cudaMemcpyDeviceToHost, s));
+    if (overlap_y) {
+        const uint64_t *yin = (const uint64_t *)ctx->d_yin + ctx->row_begin;
+        for (int k = 0; k < Y_CHUNKS; k++) {
+            const uint64_t r0 = (uint64_t)ctx->local_rows * k / Y_CHUNKS, r1 = (uint64_t)ctx->local_rows * (k + 1) / Y_CHUNKS;
+            if (r1 == r0) continue;
+            B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_ychunk[k], 0));
+            const unsigned grid = (unsigned)std::min<uint64_t>(b2_div_up(r1 - r0, 256), (uint64_t)ctx->sms * 16);
+            if (ctx->dtype == B200SPMV_F64) vec_accumulate_kernel<B200SPMV_F64><<<grid, 256, 0, s>>>(yd + r0, yin + r0, r1 - r0);
+            else vec_accumulate_kernel<B200SPMV_U64><<<grid, 256, 0, s>>>(yd + r0, yin + r0, r1 - r0);
+            B2_CHECK(ctx, cudaGetLastError());
+            ctx->launches += 1;
+            B2_CHECK(ctx, cudaMemcpyAsync(yh + r0, yd + r0, (size_t)(r1 - r0) * 8, cudaMemcpyDeviceToHost, s));
+        }
+    } else {
+        B2_CHECK(ctx, cudaMemcpyAsync(yh, yd, (size_t)ctx->local_rows * 8, cudaMemcpyDeviceToHost, s));
+    }
     B2_CHECK(ctx, cudaStreamSynchronize(s));
     float ms = 0.f;
     B2_CHECK(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));

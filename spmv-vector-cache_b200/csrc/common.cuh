@@ -12,6 +12,7 @@
 #include "../../include/b200spmv.h"
 
 struct ncclComm;
+constexpr int Y_CHUNKS = 8;  // b200spmv_exec: row chunks of the y upload / accumulate / download pipeline
 
 // ---------------------------------------------------------------------------------------
 // Device-resident matrix, one per context.
@@ -91,7 +92,9 @@ struct b200spmv_ctx {
     // [row_begin,row_end) is written by this rank)
     void *d_x = nullptr, *d_y = nullptr;
     void *d_yin = nullptr;        // the caller's y while t = A*x is computed (b200spmv_exec, accumulate)
-    cudaEvent_t ev_yin = nullptr;
+    cudaEvent_t ev_ychunk[8] = {nullptr};  // chunk k of the caller's y has landed in d_yin
+    cudaEvent_t ev_slab[64] = {nullptr};  // slice s of x has landed (b200spmv_exec uploads x slab by slab)
+    bool wait_slab_events = false;
     cudaEvent_t ev_x0 = nullptr, ev_x1 = nullptr;  // around the x exchange of the last power-iteration step
     uint64_t xchgtime_ns = 0;
     void *pin_x = nullptr, *pin_y = nullptr;  // pinned staging for pageable host vectors

@@ -1064,6 +1064,7 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
     for (int sl = 0; sl < ctx->slabs; sl++) {
         const uint32_t *rowptr = m.rowptr + sl * stride;
         const bool read_y = accumulate || sl > 0;
+        if (ctx->wait_slab_events) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_slab[sl], 0));
         if (persist != ctx->persist_set || ctx->slabs > 1) {
             const size_t c0 = (size_t)sl * ctx->slab_cols;
             const size_t c1 = std::min<size_t>(ctx->cols, c0 + ctx->slab_cols);
