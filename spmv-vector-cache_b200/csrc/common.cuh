@@ -56,7 +56,7 @@ struct b200spmv_ctx {
     int opt_keep_csc = 0;
     int opt_kernel = 3;           // 1 = merge-path LDG-staged, 2 = merge-path TMA-staged, 3 = flagged segmented sum,
                                   // 4 = flagged, persistent CTAs with a TMA-fed shared-memory ring, 5 = flagged, warp-sized tiles
-    int opt_dcsr_x16 = 32;        // slabs with < this/16 entries per non-empty row use spmv_dcsr_kernel (0 = never)
+    int opt_dcsr_x16 = 96;        // slabs with < this/16 (= 6) entries per non-empty row use spmv_dcsr_kernel (0 = never)
     int opt_prefetch_tiles = 148; // kernel 3: L2 bulk prefetch (UBLKPF) of the tile this many CTAs ahead (0 = off)
     int opt_ablate = 0;           // kernel 5 only, measurement: see spmv_flag_warp_kernel
     int opt_ctas_per_sm = 4;      // persistent grid of kernel 4 = sms * this

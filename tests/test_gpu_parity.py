@@ -25,7 +25,8 @@ def b2():
     return b200spmv
 
 
-@pytest.fixture(params=[(5, 8), (4, 8), (3, 8), (3, 16), (2, 8), (1, 8)], ids=["warp", "ring", "flag8", "flag16", "tma", "ldg"])
+@pytest.fixture(params=[(5, 8, 0), (4, 8, 0), (3, 8, 0), (3, 16, 0), (2, 8, 0), (1, 8, 0), (3, 8, 96), (3, 8, 1 << 20)],
+                ids=["warp", "ring", "flag8", "flag16", "tma", "ldg", "default", "dcsr-always"])
 def eng(b2, request):
     """all throughput kernels: 5 = flagged, warp-sized tiles (default), 4 = flagged, persistent CTAs + TMA ring,
     3 = flagged segmented sum,
@@ -33,6 +34,9 @@ def eng(b2, request):
     e = b2.Engine(0)
     e.set_option("kernel", request.param[0])
     e.set_option("ept", request.param[1])
+    # 0: never hand a slab to the thread-per-row kernel, so the kernel under test sees every matrix;
+    # 96: the shipped threshold (< 6 entries per non-empty row); 1 << 20: every slab goes to spmv_dcsr_kernel
+    e.set_option("dcsr_x16", request.param[2])
     yield e
     e.close()
 
