@@ -215,6 +215,8 @@ def run_ours(args):
         eng.set_option("ctas_per_sm", args.ctas)
     if args.prefetch is not None:
         eng.set_option("prefetch_tiles", args.prefetch)
+    if args.graph is not None:
+        eng.set_option("graph", args.graph)
     if args.ablate:
         eng.set_option("ablate", args.ablate)
     t0 = time.perf_counter()
@@ -337,6 +339,7 @@ def main():
     ap.add_argument("--kernel", type=int, default=0,
                     help="1 merge-path LDG-staged, 2 merge-path TMA-staged, 3 flagged, 4 flagged persistent TMA ring (default)")
     ap.add_argument("--prefetch", type=int, default=None, help="kernel 3: L2 bulk prefetch distance in tiles")
+    ap.add_argument("--graph", type=int, default=None, help="0: do not replay a CUDA graph in exec_device")
     ap.add_argument("--ablate", type=int, default=0, help="kernel 5 ablation level (measurement only; results are wrong)")
     ap.add_argument("--ctas", type=int, default=0, help="persistent CTAs per SM of kernel 4")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")

@@ -97,6 +97,7 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "kernel") { if (value < 1 || value > 5) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 1..5"); ctx->opt_kernel = (int)value; }
     else if (k == "dcsr_x16") ctx->opt_dcsr_x16 = (int)value;
     else if (k == "prefetch_tiles") ctx->opt_prefetch_tiles = (int)std::max<int64_t>(0, value);
+    else if (k == "graph") ctx->opt_graph = (int)value;
     else if (k == "ablate") ctx->opt_ablate = (int)value;
     else if (k == "ctas_per_sm") { if (value < 1 || value > 8) return b2_fail(ctx, B200SPMV_EINVAL, "ctas_per_sm must be 1..8"); ctx->opt_ctas_per_sm = (int)value; }
     else if (k == "world" || k == "rank") {
@@ -335,10 +336,35 @@ extern "C" int b200spmv_exec_device(b200spmv_ctx *ctx, int iters, int flags, flo
     std::vector<cudaEvent_t> ev((size_t)iters + 1);
     for (auto &e : ev) B2_CHECK(ctx, cudaEventCreate(&e));
     int rc = 0;
+    // Several back-to-back SpMVs: the launches of one step (2 per slab) are captured once into a CUDA graph
+    // and replayed, so a step costs one launch from the host (matters when a rank's block is small: 8 GPUs).
+    cudaGraphExec_t gexec = nullptr;
+    if (iters > 1 && !ctx->opt_profile && ctx->opt_graph) {
+        rc = b2_spmv_prepare(ctx, flags, s);  // stream attributes are set outside the capture
+        if (rc == 0) {
+            cudaGraph_t g = nullptr;
+            const uint64_t launches0 = ctx->launches;
+            if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+                const int rc2 = b2_spmv_launch(ctx, flags, s);
+                const cudaError_t ec = cudaStreamEndCapture(s, &g);
+                if (rc2 != 0 || ec != cudaSuccess || cudaGraphInstantiate(&gexec, g, 0) != cudaSuccess) gexec = nullptr;
+                if (g) cudaGraphDestroy(g);
+                cudaGetLastError();
+            }
+            ctx->launches_per_step = ctx->launches - launches0;
+            ctx->launches = launches0;  // the captured pass did not run
+            cudaStreamSynchronize(s);
+        }
+    }
     cudaEventRecord(ev[0], s);
     for (int i = 0; i < iters && rc == 0; i++) {
         if (ctx->opt_profile && ctx->prof_n + 2 * ctx->slabs > 128) { cudaStreamSynchronize(s); b2_profile_collect(ctx); }
-        rc = b2_spmv_launch(ctx, flags, s);
+        if (gexec) {
+            if (cudaGraphLaunch(gexec, s) != cudaSuccess) rc = b2_fail(ctx, B200SPMV_ECUDA, "graph launch failed");
+            ctx->launches += ctx->launches_per_step;
+        } else {
+            rc = b2_spmv_launch(ctx, flags, s);
+        }
         cudaEventRecord(ev[i + 1], s);
     }
     cudaError_t e = cudaStreamSynchronize(s);
@@ -352,6 +378,7 @@ extern "C" int b200spmv_exec_device(b200spmv_ctx *ctx, int iters, int flags, flo
         ctx->spmvtime_ns = (uint64_t)((double)last * 1e6);
     }
     for (auto &x : ev) cudaEventDestroy(x);
+    if (gexec) cudaGraphExecDestroy(gexec);
     return rc;
 }
 

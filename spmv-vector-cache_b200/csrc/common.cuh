@@ -58,6 +58,7 @@ struct b200spmv_ctx {
                                   // 4 = flagged, persistent CTAs with a TMA-fed shared-memory ring, 5 = flagged, warp-sized tiles
     int opt_dcsr_x16 = 96;        // slabs with < this/16 (= 6) entries per non-empty row use spmv_dcsr_kernel (0 = never)
     int opt_prefetch_tiles = 148; // kernel 3: L2 bulk prefetch (UBLKPF) of the tile this many CTAs ahead (0 = off)
+    int opt_graph = 1;            // b200spmv_exec_device replays a captured CUDA graph of one step
     int opt_ablate = 0;           // kernel 5 only, measurement: see spmv_flag_warp_kernel
     int opt_ctas_per_sm = 4;      // persistent grid of kernel 4 = sms * this
     int opt_ept = 8;              // entries per thread of kernel 3 (8 or 16)
@@ -110,6 +111,7 @@ struct b200spmv_ctx {
     // stats
     uint64_t spmvtime_ns = 0, xfertime_ns = 0, setuptime_ns = 0, transposetime_ns = 0;
     uint64_t launches = 0;
+    uint64_t launches_per_step = 0;
     cudaEvent_t prof_ev[128] = {nullptr};
     int prof_n = 0;               // events recorded since the last read
     uint64_t merge_kernel_ns = 0, merge_kernel_launches = 0;
@@ -183,6 +185,7 @@ int b2_build_tiles(b200spmv_ctx *ctx);
 int b2_build_flags(b200spmv_ctx *ctx);
 constexpr uint32_t B2_FLAG_TILE = 2048;  // entries per CTA of the flagged kernel; slabs are padded to it
 int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s);
+int b2_spmv_prepare(b200spmv_ctx *ctx, int flags, cudaStream_t s);
 void b2_profile_collect(b200spmv_ctx *ctx);
 // synth.cu
 int b2_synth_build_csc(b200spmv_ctx *ctx, int kind, uint32_t npr, uint64_t seed);

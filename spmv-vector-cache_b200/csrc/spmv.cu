@@ -1065,12 +1065,6 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
         const uint32_t *rowptr = m.rowptr + sl * stride;
         const bool read_y = accumulate || sl > 0;
         if (ctx->wait_slab_events) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_slab[sl], 0));
-        if (persist != ctx->persist_set || ctx->slabs > 1) {
-            const size_t c0 = (size_t)sl * ctx->slab_cols;
-            const size_t c1 = std::min<size_t>(ctx->cols, c0 + ctx->slab_cols);
-            B2_TRY(set_persist_window(ctx, s, x + c0, (c1 - c0) * 8, persist));
-            ctx->persist_set = persist;
-        }
         if (!strict && ctx->opt_kernel >= 3 && ctx->flagged) {
             const uint32_t tb = ctx->h_ftile_base[sl];
             const uint32_t nt = ctx->h_ftile_base[sl + 1] - tb;
@@ -1216,8 +1210,17 @@ void b2_profile_collect(b200spmv_ctx *ctx)
     ctx->prof_n = 0;
 }
 
-int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s)
+// Everything a launch needs that is not a stream operation (safe to call before a graph capture).
+// The access-policy window is a stream attribute: set when the mode changes, not per launch.  It covers the
+// whole of x up to the device's window limit; which slice is hot is decided by the slab being processed,
+// the window only marks x as the data to keep (profiles/r01_gather_paths.txt, A/B).
+int b2_spmv_prepare(b200spmv_ctx *ctx, int flags, cudaStream_t s)
 {
+    const bool persist = !(flags & B200SPMV_NO_PERSIST);
+    if (persist != ctx->persist_set) {
+        B2_TRY(set_persist_window(ctx, s, ctx->d_x, (size_t)ctx->cols * 8, persist));
+        ctx->persist_set = persist;
+    }
     static bool carveout_set = false;
     if (!carveout_set) {
 #define B2_CARVE(DT) \
@@ -1234,6 +1237,12 @@ int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s)
 #undef B2_CARVE
         carveout_set = true;
     }
+    return 0;
+}
+
+int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s)
+{
+    B2_TRY(b2_spmv_prepare(ctx, flags, s));
     return ctx->dtype == B200SPMV_F64 ? launch_dtype<B200SPMV_F64>(ctx, flags, s)
                                       : launch_dtype<B200SPMV_U64>(ctx, flags, s);
 }
