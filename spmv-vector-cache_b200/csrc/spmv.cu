@@ -428,16 +428,26 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
         if (close_row >= rows) close_row = NO_ROW;
         if (READ_Y && close_row != NO_ROW) y_old = y[close_row];
     }
+    // a second flag in my entries closes a row that lies wholly inside them: its row id and y are fetched
+    // now as well (rows shorter than 8 entries are common once a matrix is cut into column slabs)
+    uint32_t row2 = NO_ROW;
+    uint64_t y_old2 = 0;
+    if (nfl > 1) {
+        row2 = HAS_EMPTY ? __ldg(seg_row + segs_before) : segs_before;
+        if (row2 >= rows) row2 = NO_ROW;
+        if (READ_Y && row2 != NO_ROW) y_old2 = y[row2];
+    }
 
     // branch-free sequential pass: head = sum before my first flag, acc = sum after my last flag
-    uint64_t acc = 0, head = 0;
+    uint64_t acc = 0, head = 0, mid = 0;  // mid = the row between my first and second flag
     uint32_t seen = 0;
 #pragma unroll
     for (int i = 0; i < EPT; i++) {
         p[i] = Semi<DT>::mul(p[i], xv[i]);
         const uint32_t fl = (f >> i) & 1u;
-        head = (fl & ~seen & 1u) ? acc : head;
-        seen |= fl;
+        head = (fl && seen == 0) ? acc : head;
+        mid = (fl && seen == 1) ? acc : mid;
+        seen += fl;
         acc = fl ? 0ull : acc;
         acc = Semi<DT>::add(acc, p[i]);
     }
@@ -472,13 +482,14 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
             if (READ_Y) val = Semi<DT>::add(y_old, val);
             y[close_row] = val;
         }
-        if (nfl > 1) {  // rows that begin and end inside my entries (short rows): re-walk
+        if (nfl > 1 && row2 != NO_ROW) y[row2] = READ_Y ? Semi<DT>::add(y_old2, mid) : mid;
+        if (nfl > 2) {  // further rows that begin and end inside my entries (very short rows): re-walk
             uint64_t a = 0;
             uint32_t k = 0;
 #pragma unroll
             for (int i = 0; i < EPT; i++) {
                 if ((f >> i) & 1u) {
-                    if (k != 0) store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before + k - 1, a);
+                    if (k > 1) store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before + k - 1, a);
                     k++;
                     a = 0;
                 }
