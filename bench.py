@@ -219,6 +219,8 @@ def run_ours(args):
         eng.set_option("prefetch_tiles", args.prefetch)
     if args.graph is not None:
         eng.set_option("graph", args.graph)
+    if args.workload == "banded-power" and world > 1 and not args.shard and not args.no_overlap:
+        eng.set_option("own_slabs", 1)  # slabs aligned with the ranks' x blocks: the exchange overlaps the own-block slabs
     if args.ablate:
         eng.set_option("ablate", args.ablate)
     t0 = time.perf_counter()
@@ -251,7 +253,7 @@ def run_ours(args):
     launches0 = eng.stat("launches")
     sampler.start()
     if power:
-        ms_total, _ = eng.power_iterate(args.steps, True, flags & ~b2.ACCUMULATE)
+        ms_total, last_norm = eng.power_iterate(args.steps, True, flags & ~b2.ACCUMULATE)
     else:
         ms = eng.exec_device(args.steps, flags)  # CUDA events on the launching stream, one pair per step
         ms_total = float(ms.sum())
@@ -304,7 +306,9 @@ def run_ours(args):
                                     "row blocks + x all-gather per step",
                        "l2": "inputs (%.1f GB) larger than L2; no flush" % (b_alg(nnz, rows, cols) / 1e9),
                        "slabs": slabs, "persist_window": not args.no_persist, "setup_s": round(setup_s, 2),
-                       **({"x_exchange_ms_last_step": eng.stat("xchgtime_ns") * 1e-6} if power and world > 1 else {})},
+                       **({"x_exchange_ms_last_step": eng.stat("xchgtime_ns") * 1e-6, "exchange_overlapped": not args.no_overlap}
+                          if power and world > 1 else {}),
+                       **({"norm_after_last_step": last_norm} if power else {})},
             "gb_s_algorithmic": b_alg(nnz, rows, cols) * args.steps / t_dev / 1e9 if world == 1 else None,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
@@ -347,6 +351,7 @@ def main():
     ap.add_argument("--ctas", type=int, default=0, help="persistent CTAs per SM of kernel 4")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
     ap.add_argument("--no-persist", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="power iteration: exchange x after the step instead of under the own-block slabs")
     ap.add_argument("--strict", action="store_true", help="strict-order kernel (fp64 memcmp-equal to SoftwareSpMV)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

@@ -76,6 +76,7 @@ extern "C" void b200spmv_destroy(b200spmv_ctx *ctx)
     for (int i = 0; i < Y_CHUNKS; i++) if (ctx->ev_ychunk[i]) cudaEventDestroy(ctx->ev_ychunk[i]);
     for (int i = 0; i < 64; i++) if (ctx->ev_slab[i]) cudaEventDestroy(ctx->ev_slab[i]);
     if (ctx->ev_x0) { cudaEventDestroy(ctx->ev_x0); cudaEventDestroy(ctx->ev_x1); }
+    if (ctx->comm_stream) { cudaStreamDestroy(ctx->comm_stream); cudaEventDestroy(ctx->ev_xready); cudaEventDestroy(ctx->ev_xdone); }
     cudaStreamDestroy(ctx->stream); cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
 }
@@ -98,6 +99,10 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "dcsr_x16") ctx->opt_dcsr_x16 = (int)value;
     else if (k == "prefetch_tiles") ctx->opt_prefetch_tiles = (int)std::max<int64_t>(0, value);
     else if (k == "graph") ctx->opt_graph = (int)value;
+    else if (k == "own_slabs") {
+        if (ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "set own_slabs before setup");
+        ctx->opt_own_slabs = value != 0;
+    }
     else if (k == "ablate") ctx->opt_ablate = (int)value;
     else if (k == "ctas_per_sm") { if (value < 1 || value > 8) return b2_fail(ctx, B200SPMV_EINVAL, "ctas_per_sm must be 1..8"); ctx->opt_ctas_per_sm = (int)value; }
     else if (k == "world" || k == "rank") {
@@ -136,16 +141,38 @@ static int csc_to_csr(b200spmv_ctx *ctx, uint32_t index_mask)
     DeviceCsr &m = ctx->csr;
     const uint64_t t0 = now_ns();
     ctx->slabs = choose_slabs(ctx);
-    ctx->slab_cols = (uint32_t)(((uint64_t)b2_div_up(ctx->cols, ctx->slabs) + 31) & ~31ull);
-    ctx->slabs = (int)b2_div_up(ctx->cols, ctx->slab_cols);
+    ctx->own_lo = ctx->own_hi = 0;
+    bool own = ctx->opt_own_slabs && ctx->world > 1 && ctx->rows == ctx->cols && ctx->h_row_splits;
+    if (own) {
+        // slabs aligned with the ranks' blocks of x: every block is cut into the same number of slabs, so that
+        // the slabs of this rank's own block can run while the other blocks are still on the wire
+        const int per_block = (int)b2_div_up((uint64_t)ctx->slabs, (uint64_t)ctx->world);
+        if (per_block * ctx->world > 64) own = false;
+        else {
+            ctx->slabs = per_block * ctx->world;
+            for (int r = 0; r < ctx->world; r++) {
+                const uint64_t b = ctx->h_row_splits[r], w = ctx->h_row_splits[r + 1] - b;
+                for (int k = 0; k < per_block; k++) ctx->h_slab_col[r * per_block + k] = (uint32_t)(b + w * k / per_block);
+            }
+            ctx->h_slab_col[ctx->slabs] = ctx->cols;
+            ctx->own_lo = ctx->rank * per_block;
+            ctx->own_hi = ctx->own_lo + per_block;
+            ctx->slab_cols = 0;
+        }
+    }
+    if (!own) {
+        ctx->slab_cols = (uint32_t)(((uint64_t)b2_div_up(ctx->cols, ctx->slabs) + 31) & ~31ull);
+        ctx->slabs = (int)b2_div_up(ctx->cols, ctx->slab_cols);
+        for (int sl = 0; sl <= ctx->slabs; sl++)
+            ctx->h_slab_col[sl] = (uint32_t)std::min<uint64_t>((uint64_t)sl * ctx->slab_cols, ctx->cols);
+    }
     ctx->rowptr_stride = ((size_t)ctx->local_rows + 1 + 3) & ~(size_t)3;
     // slab entry ranges in the CSC (columns are contiguous there), each padded to a whole number
     // of flagged-kernel tiles plus at least one pad entry (the sentinel that closes the last row)
     std::vector<uint32_t> e0(ctx->slabs), e1(ctx->slabs);
     uint64_t off = 0;
     for (int sl = 0; sl < ctx->slabs; sl++) {
-        const uint32_t c0 = (uint32_t)std::min<uint64_t>((uint64_t)sl * ctx->slab_cols, ctx->cols);
-        const uint32_t c1 = (uint32_t)std::min<uint64_t>((uint64_t)c0 + ctx->slab_cols, ctx->cols);
+        const uint32_t c0 = ctx->h_slab_col[sl], c1 = ctx->h_slab_col[sl + 1];
         B2_CHECK(ctx, cudaMemcpyAsync(&e0[sl], ctx->csc_colptr + c0, 4, cudaMemcpyDeviceToHost, s));
         B2_CHECK(ctx, cudaMemcpyAsync(&e1[sl], ctx->csc_colptr + c1, 4, cudaMemcpyDeviceToHost, s));
         B2_CHECK(ctx, cudaStreamSynchronize(s));
@@ -267,7 +294,7 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
     const bool sliced_x = ctx->slabs > 1 && !(flags & B200SPMV_STRICT_ORDER) && (size_t)ctx->cols * 8 >= (8u << 20);
     if (sliced_x) {
         for (int sl = 0; sl < ctx->slabs; sl++) {
-            const size_t c0 = (size_t)sl * ctx->slab_cols, c1 = std::min<size_t>(ctx->cols, c0 + ctx->slab_cols);
+            const size_t c0 = ctx->h_slab_col[sl], c1 = ctx->h_slab_col[sl + 1];
             if (!ctx->ev_slab[sl]) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_slab[sl], cudaEventDisableTiming));
             B2_CHECK(ctx, cudaMemcpyAsync((uint64_t *)ctx->d_x + c0, (const uint64_t *)x_host + c0, (c1 - c0) * 8,
                                           cudaMemcpyHostToDevice, ctx->copy_stream));

@@ -58,6 +58,7 @@ struct b200spmv_ctx {
                                   // 4 = flagged, persistent CTAs with a TMA-fed shared-memory ring, 5 = flagged, warp-sized tiles
     int opt_dcsr_x16 = 96;        // slabs with < this/16 (= 6) entries per non-empty row use spmv_dcsr_kernel (0 = never)
     int opt_prefetch_tiles = 148; // kernel 3: L2 bulk prefetch (UBLKPF) of the tile this many CTAs ahead (0 = off)
+    int opt_own_slabs = 0;        // 1: align the slabs with the ranks' blocks of x (set before setup; see own_lo)
     int opt_graph = 1;            // b200spmv_exec_device replays a captured CUDA graph of one step
     int opt_ablate = 0;           // kernel 5 only, measurement: see spmv_flag_warp_kernel
     int opt_ctas_per_sm = 4;      // persistent grid of kernel 4 = sms * this
@@ -74,7 +75,15 @@ struct b200spmv_ctx {
     size_t rowptr_stride = 0;     // elements between the slabs' row-pointer arrays (multiple of 4)
     uint64_t local_nnz = 0;
     int slabs = 1;
-    uint32_t slab_cols = 0;       // columns per slab (last may be short)
+    uint32_t slab_cols = 0;       // columns per slab (last may be short) when the slabs are uniform
+    uint32_t h_slab_col[65] = {0};     // column boundaries of the slabs
+    // iterated SpMV over several ranks (option own_slabs): slabs [own_lo, own_hi) cover exactly this rank's own
+    // block of x; b2_spmv_launch runs them first and waits on ev_rest (the arrival of the other blocks) before
+    // the remaining slabs
+    int own_lo = 0, own_hi = 0;
+    cudaEvent_t ev_rest = nullptr;     // non-null only while b200spmv_power_iterate overlaps the exchange
+    cudaEvent_t ev_xready = nullptr, ev_xdone = nullptr;
+    cudaStream_t comm_stream = nullptr;
     uint32_t h_tile_base[65] = {0};
     uint32_t h_ftile_base[65] = {0};   // flagged-kernel tiles per slab (prefix)
     uint64_t h_slab_off[65] = {0};     // entry offset of each slab in colind/vals (padded to FLAG_TILE)

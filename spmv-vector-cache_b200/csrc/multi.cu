@@ -280,9 +280,26 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
     const int spmv_flags = flags & ~B200SPMV_ACCUMULATE;  // y = A*x each step
     uint64_t *yb = (uint64_t *)ctx->d_y + ctx->row_begin;
     uint64_t *xb = (uint64_t *)ctx->d_x + ctx->row_begin;
+    // Overlap of the exchange with the next step (setup option own_slabs): the slabs that cover this rank's own
+    // block of x only gather what scale_into_x has just written, so they run on the compute stream while the
+    // all-gather of the other blocks is still in flight on a second, higher-priority stream; the remaining slabs
+    // wait for its event.  Strict order keeps the slabs in column order and therefore does not overlap.
+    const bool overlap = ctx->world > 1 && ctx->own_hi > ctx->own_lo && !(flags & B200SPMV_STRICT_ORDER);
+    if (overlap && !ctx->comm_stream) {
+        int lo = 0, hi = 0;
+        B2_CHECK(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        B2_CHECK(ctx, cudaStreamCreateWithPriority(&ctx->comm_stream, cudaStreamNonBlocking, hi));
+        B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_xready, cudaEventDisableTiming));
+        B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_xdone, cudaEventDisableTiming));
+    }
+    cudaStream_t xs = overlap ? ctx->comm_stream : s;
+    bool in_flight = false;
     B2_CHECK(ctx, cudaEventRecord(ctx->ev0, s));
     for (int it = 0; it < steps; it++) {
-        B2_TRY(b2_spmv_launch(ctx, spmv_flags, s));
+        ctx->ev_rest = in_flight ? ctx->ev_xdone : nullptr;
+        const int rc = b2_spmv_launch(ctx, spmv_flags, s);
+        ctx->ev_rest = nullptr;
+        if (rc) return rc;
         if (!is_u64) {
             sumsq_partial_kernel<<<RED_BLOCKS, RED_THREADS, 0, s>>>((const double *)yb, ctx->local_rows, partial);
             sumsq_final_kernel<<<1, RED_THREADS, 0, s>>>(partial, RED_BLOCKS, norm2);
@@ -291,13 +308,22 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
         scale_into_x_kernel<<<ctx->sms * 8, 256, 0, s>>>(yb, ctx->local_rows, norm2, is_u64, xb);
         ctx->launches += is_u64 ? 1 : 3;
         const bool timed = it == steps - 1 && ctx->world > 1;  // exchange time of the last step -> stat "xchgtime_ns"
+        if (overlap) {
+            B2_CHECK(ctx, cudaEventRecord(ctx->ev_xready, s));
+            B2_CHECK(ctx, cudaStreamWaitEvent(xs, ctx->ev_xready, 0));
+        }
         if (timed) {
             if (!ctx->ev_x0) { B2_CHECK(ctx, cudaEventCreate(&ctx->ev_x0)); B2_CHECK(ctx, cudaEventCreate(&ctx->ev_x1)); }
-            B2_CHECK(ctx, cudaEventRecord(ctx->ev_x0, s));
+            B2_CHECK(ctx, cudaEventRecord(ctx->ev_x0, xs));
         }
-        B2_TRY(allgather_x(ctx, s));
-        if (timed) B2_CHECK(ctx, cudaEventRecord(ctx->ev_x1, s));
+        B2_TRY(allgather_x(ctx, xs));
+        if (timed) B2_CHECK(ctx, cudaEventRecord(ctx->ev_x1, xs));
+        if (overlap) {
+            B2_CHECK(ctx, cudaEventRecord(ctx->ev_xdone, xs));
+            in_flight = true;
+        }
     }
+    if (in_flight) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_xdone, 0));  // x is whole again when the call returns
     B2_CHECK(ctx, cudaEventRecord(ctx->ev1, s));
     B2_CHECK(ctx, cudaStreamSynchronize(s));
     float ms = 0.f;

@@ -1072,9 +1072,20 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
     const size_t stride = ctx->rowptr_stride;
     const uint32_t rows = ctx->local_rows;
     if (rows == 0) return 0;
-    for (int sl = 0; sl < ctx->slabs; sl++) {
+    // slab order: this rank's own block of x first when the caller overlaps the exchange of the other blocks
+    const int n_own = ctx->ev_rest ? ctx->own_hi - ctx->own_lo : 0;
+    for (int pos = 0; pos < ctx->slabs; pos++) {
+        int sl = pos;
+        if (n_own > 0) {
+            if (pos < n_own) sl = ctx->own_lo + pos;
+            else {
+                sl = pos - n_own;
+                if (sl >= ctx->own_lo) sl += n_own;
+                if (pos == n_own) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_rest, 0));
+            }
+        }
         const uint32_t *rowptr = m.rowptr + sl * stride;
-        const bool read_y = accumulate || sl > 0;
+        const bool read_y = accumulate || pos > 0;
         if (ctx->wait_slab_events) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_slab[sl], 0));
         if (!strict && ctx->opt_kernel >= 3 && ctx->flagged) {
             const uint32_t tb = ctx->h_ftile_base[sl];

@@ -70,3 +70,34 @@ def test_synthetic_sharded_equals_whole(kind, rows, npr):
         e.close()
     assert sum(per) == nnz
     assert y.tobytes() == want.tobytes()
+
+
+@pytest.mark.parametrize("name,dtype,world,slabs", [("circuit204", "u64", 3, 0), ("circuit204", "f64", 2, 4), ("i64k", "u64", 8, 0),
+                                                    ("i64k", "f64", 4, 6)])
+def test_slabs_aligned_with_the_ranks_blocks(oracle, name, dtype, world, slabs):
+    """option own_slabs: the column slabs follow the ranks' blocks of x (what lets the iterated SpMV overlap the
+    exchange); a single SpMV over such slabs must still be the reference product, strict order included."""
+    import b200spmv as b2
+    m = H.load_matrix_dir(os.path.join(H.MATRICES, name))
+    vals = H.rand_values(m.nnz, dtype, 31)
+    x = H.make_x(m.cols, dtype, "rand", 32)
+    npdt = np.uint64 if dtype == "u64" else np.float64
+    want = np.zeros(m.rows, dtype=npdt)
+    oracle.spmv_csc(dtype, m.rows, m.cols, m.colptr, m.rowind, vals, x, want)
+    for flags in (b2.ACCUMULATE | b2.STRICT_ORDER, b2.ACCUMULATE):
+        y = np.zeros(m.rows, dtype=npdt)
+        for r in range(world):
+            e = b2.Engine(0)
+            e.set_option("world", world)
+            e.set_option("rank", r)
+            e.set_option("own_slabs", 1)
+            if slabs:
+                e.set_option("slabs", slabs)
+            e.setup_csc(m.rows, m.cols, m.colptr, m.rowind, vals, b2.U64 if dtype == "u64" else b2.F64)
+            assert e.stat("slabs") % world == 0
+            e.exec(x, y, flags)
+            e.close()
+        if dtype == "u64" or flags & b2.STRICT_ORDER:
+            assert y.tobytes() == want.tobytes()
+        else:
+            assert np.allclose(y, want, rtol=1e-12, atol=1e-12 * float(np.max(np.abs(want))))

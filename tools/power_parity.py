@@ -1,0 +1,75 @@
+#!/usr/bin/env python
+"""Iterated SpMV over several GPUs against the same iteration on one GPU (run under torchrun, >= 2 ranks).
+
+Every rank builds (a) its row block of a banded+random matrix with the slabs aligned to the ranks' x blocks, so
+that b200spmv_power_iterate overlaps the all-gather of x with the slabs of its own block, (b) the same block
+without the overlap, (c) the whole matrix alone.  After K steps the replicated x of (a) and (b) must equal the x
+of (c): bit for bit for uint64, to 1e-12 relative for fp64 (the slabs are summed in another order).
+"""
+import importlib.util
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+spec = importlib.util.spec_from_file_location("b200spmv", os.path.join(ROOT, "spmv-vector-cache_b200", "b200spmv.py"))
+b2 = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(b2)
+
+
+def make(local, rank, world, dtype, rows, npr, slabs, own):
+    e = b2.Engine(local)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(b2.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        e.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
+        if own:
+            e.set_option("own_slabs", 1)
+    if slabs:
+        e.set_option("slabs", slabs)
+    e.setup_synthetic(2, rows, rows, npr, 12345, dtype)
+    return e
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    bad = 0
+    for dtype, name in ((b2.F64, "f64"), (b2.U64, "u64")):
+        for rows, slabs in ((1 << 20, 0), (1 << 20, 4), ((1 << 20) + 8 * 977, 3), (1 << 22, 0)):
+            steps = 6 if dtype == b2.F64 else 3
+            single = make(local, 0, 1, dtype, rows, 5, slabs, False)
+            single.power_iterate(steps, False, 0)
+            want = single.get_x()
+            del single
+            for own in (True, False):
+                e = make(local, rank, world, dtype, rows, 5, slabs, own)
+                _, nrm = e.power_iterate(steps, False, 0)
+                # a second call continues from the replicated x (what bench.py does after its warm-up)
+                got = e.get_x()
+                if dtype == b2.U64:
+                    ok = np.array_equal(got, want)
+                    err = int((got != want).sum())
+                else:
+                    err = float(np.max(np.abs(got - want)) / np.max(np.abs(want)))
+                    ok = err < 1e-12
+                print("rank %d %s rows %d slabs opt %d -> %d own_slabs %d: %s (%s)" %
+                      (rank, name, rows, slabs, e.stat("slabs"), own, "ok" if ok else "MISMATCH", err), flush=True)
+                bad += not ok
+                del e
+    t = torch.tensor([bad], device="cuda")
+    dist.all_reduce(t)
+    if rank == 0:
+        print("POWER PARITY %s" % ("OK" if int(t.item()) == 0 else "FAILED"), flush=True)
+    dist.destroy_process_group()
+    sys.exit(1 if int(t.item()) else 0)
+
+
+if __name__ == "__main__":
+    main()
