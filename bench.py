@@ -219,8 +219,12 @@ def run_ours(args):
         eng.set_option("prefetch_tiles", args.prefetch)
     if args.graph is not None:
         eng.set_option("graph", args.graph)
-    if args.workload == "banded-power" and world > 1 and not args.shard and not args.no_overlap:
-        eng.set_option("own_slabs", 1)  # slabs aligned with the ranks' x blocks: the exchange overlaps the own-block slabs
+    if args.workload == "banded-power" and world > 1 and not args.shard and args.exchange != "nccl":
+        # slabs aligned with the ranks' x blocks: the exchange of the other blocks runs under the own-block slabs
+        eng.set_option("own_slabs", 1)
+        eng.set_option("exchange", 2 if args.exchange == "pull" else 1)
+        if args.pull_streams:
+            eng.set_option("pull_streams", args.pull_streams)
     if args.ablate:
         eng.set_option("ablate", args.ablate)
     t0 = time.perf_counter()
@@ -306,7 +310,8 @@ def run_ours(args):
                                     "row blocks + x all-gather per step",
                        "l2": "inputs (%.1f GB) larger than L2; no flush" % (b_alg(nnz, rows, cols) / 1e9),
                        "slabs": slabs, "persist_window": not args.no_persist, "setup_s": round(setup_s, 2),
-                       **({"x_exchange_ms_last_step": eng.stat("xchgtime_ns") * 1e-6, "exchange_overlapped": not args.no_overlap}
+                       **({"x_exchange_ms_last_step": eng.stat("xchgtime_ns") * 1e-6, "exchange": ["NCCL all-gather after the step", "NCCL all-gather under the own-block slabs",
+                                        "peer pulls block by block under the slabs"][eng.stat("exchange_mode")]}
                           if power and world > 1 else {}),
                        **({"norm_after_last_step": last_norm} if power else {})},
             "gb_s_algorithmic": b_alg(nnz, rows, cols) * args.steps / t_dev / 1e9 if world == 1 else None,
@@ -351,7 +356,9 @@ def main():
     ap.add_argument("--ctas", type=int, default=0, help="persistent CTAs per SM of kernel 4")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
     ap.add_argument("--no-persist", action="store_true")
-    ap.add_argument("--no-overlap", action="store_true", help="power iteration: exchange x after the step instead of under the own-block slabs")
+    ap.add_argument("--exchange", choices=["pull", "overlap", "nccl"], default="pull",
+                    help="power iteration over several GPUs: how the replicated x is refreshed (DESIGN.md section 7)")
+    ap.add_argument("--pull-streams", type=int, default=0)
     ap.add_argument("--strict", action="store_true", help="strict-order kernel (fp64 memcmp-equal to SoftwareSpMV)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

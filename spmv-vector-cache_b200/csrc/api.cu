@@ -24,6 +24,7 @@ static void release_matrix(b200spmv_ctx *ctx)
     { uint64_t *v = (uint64_t *)m.carry_val; b2_free(v); m.carry_val = nullptr; }
     b2_free(ctx->csc_colptr); b2_free(ctx->csc_rowind);
     { uint64_t *v = (uint64_t *)ctx->csc_vals; b2_free(v); ctx->csc_vals = nullptr; }
+    b2_close_peers(ctx);
     { uint64_t *v = (uint64_t *)ctx->d_x; b2_free(v); ctx->d_x = nullptr; }
     { uint64_t *v = (uint64_t *)ctx->d_y; b2_free(v); ctx->d_y = nullptr; }
     { uint64_t *v = (uint64_t *)ctx->d_yin; b2_free(v); ctx->d_yin = nullptr; }
@@ -76,7 +77,9 @@ extern "C" void b200spmv_destroy(b200spmv_ctx *ctx)
     for (int i = 0; i < Y_CHUNKS; i++) if (ctx->ev_ychunk[i]) cudaEventDestroy(ctx->ev_ychunk[i]);
     for (int i = 0; i < 64; i++) if (ctx->ev_slab[i]) cudaEventDestroy(ctx->ev_slab[i]);
     if (ctx->ev_x0) { cudaEventDestroy(ctx->ev_x0); cudaEventDestroy(ctx->ev_x1); }
-    if (ctx->comm_stream) { cudaStreamDestroy(ctx->comm_stream); cudaEventDestroy(ctx->ev_xready); cudaEventDestroy(ctx->ev_xdone); }
+    if (ctx->comm_stream) { cudaStreamDestroy(ctx->comm_stream); cudaEventDestroy(ctx->ev_xready); cudaEventDestroy(ctx->ev_xdone); cudaEventDestroy(ctx->ev_bar); }
+    for (int i = 0; i < 4; i++) if (ctx->pull_stream[i]) cudaStreamDestroy(ctx->pull_stream[i]);
+    for (int i = 0; i < 64; i++) if (ctx->ev_blk[i]) cudaEventDestroy(ctx->ev_blk[i]);
     cudaStreamDestroy(ctx->stream); cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
 }
@@ -99,6 +102,8 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "dcsr_x16") ctx->opt_dcsr_x16 = (int)value;
     else if (k == "prefetch_tiles") ctx->opt_prefetch_tiles = (int)std::max<int64_t>(0, value);
     else if (k == "graph") ctx->opt_graph = (int)value;
+    else if (k == "exchange") { if (value < 1 || value > 2) return b2_fail(ctx, B200SPMV_EINVAL, "exchange must be 1 or 2"); ctx->opt_exchange = (int)value; }
+    else if (k == "pull_streams") { if (value < 1 || value > 4) return b2_fail(ctx, B200SPMV_EINVAL, "pull_streams must be 1..4"); ctx->opt_pull_streams = (int)value; }
     else if (k == "own_slabs") {
         if (ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "set own_slabs before setup");
         ctx->opt_own_slabs = value != 0;
@@ -505,6 +510,7 @@ extern "C" int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *o
     else if (k == "setuptime_ns") *out = ctx->setuptime_ns;
     else if (k == "transposetime_ns") *out = ctx->transposetime_ns;
     else if (k == "xchgtime_ns") *out = ctx->xchgtime_ns;
+    else if (k == "exchange_mode") *out = (uint64_t)ctx->exchange_mode;
     else if (k == "slabs") *out = (uint64_t)ctx->slabs;
     else if (k == "l2_persist_bytes") *out = ctx->max_persist_bytes;
     else if (k == "l2_bytes") *out = ctx->l2_bytes;

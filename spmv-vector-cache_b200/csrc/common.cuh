@@ -59,6 +59,8 @@ struct b200spmv_ctx {
     int opt_dcsr_x16 = 96;        // slabs with < this/16 (= 6) entries per non-empty row use spmv_dcsr_kernel (0 = never)
     int opt_prefetch_tiles = 148; // kernel 3: L2 bulk prefetch (UBLKPF) of the tile this many CTAs ahead (0 = off)
     int opt_own_slabs = 0;        // 1: align the slabs with the ranks' blocks of x (set before setup; see own_lo)
+    int opt_exchange = 2;         // with own_slabs: 1 = NCCL all-gather under the own-block slabs, 2 = peer pulls
+    int opt_pull_streams = 2;     // copy streams the peer pulls are spread over
     int opt_graph = 1;            // b200spmv_exec_device replays a captured CUDA graph of one step
     int opt_ablate = 0;           // kernel 5 only, measurement: see spmv_flag_warp_kernel
     int opt_ctas_per_sm = 4;      // persistent grid of kernel 4 = sms * this
@@ -78,12 +80,20 @@ struct b200spmv_ctx {
     uint32_t slab_cols = 0;       // columns per slab (last may be short) when the slabs are uniform
     uint32_t h_slab_col[65] = {0};     // column boundaries of the slabs
     // iterated SpMV over several ranks (option own_slabs): slabs [own_lo, own_hi) cover exactly this rank's own
-    // block of x; b2_spmv_launch runs them first and waits on ev_rest (the arrival of the other blocks) before
-    // the remaining slabs
+    // block of x.  b200spmv_power_iterate then hands b2_spmv_launch an explicit slab order (own block first, the
+    // other blocks in the order they arrive) and, per position, an event to wait on before that slab starts.
     int own_lo = 0, own_hi = 0;
-    cudaEvent_t ev_rest = nullptr;     // non-null only while b200spmv_power_iterate overlaps the exchange
-    cudaEvent_t ev_xready = nullptr, ev_xdone = nullptr;
+    int order_n = 0;                   // == slabs while an order is in force, else 0
+    int h_order[64] = {0};             // slab run at position p
+    cudaEvent_t slab_wait[64] = {nullptr};  // by position; nullptr = no wait
+    cudaEvent_t ev_xready = nullptr, ev_xdone = nullptr, ev_bar = nullptr;
+    cudaEvent_t ev_blk[64] = {nullptr};     // block r of x has landed (peer pulls)
     cudaStream_t comm_stream = nullptr;
+    cudaStream_t pull_stream[4] = {nullptr};
+    void *x_peer[64] = {nullptr};      // the other ranks' d_x, mapped through CUDA IPC
+    bool peers_open = false, peers_failed = false;
+    int exchange_mode = 0;             // what the last power iteration did: 0 after the step (NCCL), 1 all-gather
+                                       // under the own-block slabs, 2 peer pulls block by block
     uint32_t h_tile_base[65] = {0};
     uint32_t h_ftile_base[65] = {0};   // flagged-kernel tiles per slab (prefix)
     uint64_t h_slab_off[65] = {0};     // entry offset of each slab in colind/vals (padded to FLAG_TILE)
@@ -201,6 +211,7 @@ int b2_synth_build_csc(b200spmv_ctx *ctx, int kind, uint32_t npr, uint64_t seed)
 int b2_synth_fill_x(b200spmv_ctx *ctx, uint64_t seed);
 // multi.cu
 int b2_comm_destroy(b200spmv_ctx *ctx);
+void b2_close_peers(b200spmv_ctx *ctx);
 int b2_shard_csc(b200spmv_ctx *ctx, uint32_t index_mask);
 
 // ---- device helpers --------------------------------------------------------------------

@@ -8,7 +8,10 @@
 #include <dlfcn.h>
 #include <math.h>
 
+#include <string.h>
+
 #include <algorithm>
+#include <vector>
 
 #include "common.cuh"
 
@@ -258,6 +261,57 @@ static int allgather_x(b200spmv_ctx *ctx, cudaStream_t s)
     return 0;
 }
 
+// CUDA IPC mappings of the other ranks' x (one process per GPU on one node): handles travel through the
+// communicator.  Failure to map (no peer access between two GPUs) is not an error: the caller falls back to the
+// NCCL all-gather and stat "exchange_mode" says so.
+static int open_peers(b200spmv_ctx *ctx)
+{
+    if (ctx->peers_open || ctx->peers_failed) return 0;
+    cudaStream_t s = ctx->stream;
+    const int W = ctx->world;
+    uint64_t *d_h = nullptr;
+    B2_TRY(b2_alloc(ctx, &d_h, (size_t)W * 8));
+    cudaIpcMemHandle_t mine;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle travels as 8 words");
+    std::vector<cudaIpcMemHandle_t> all(W);
+    memset(&mine, 0, sizeof mine);
+    const bool got = cudaIpcGetMemHandle(&mine, ctx->d_x) == cudaSuccess;
+    if (!got) { cudaGetLastError(); memset(&mine, 0, sizeof mine); }
+    B2_CHECK(ctx, cudaMemcpyAsync(d_h + (size_t)ctx->rank * 8, &mine, 64, cudaMemcpyHostToDevice, s));
+    NCCL_TRY(ctx, g_nccl.allgather(d_h + (size_t)ctx->rank * 8, d_h, 8, NCCL_UINT64, ctx->comm, s));
+    B2_CHECK(ctx, cudaMemcpyAsync(all.data(), d_h, (size_t)W * 64, cudaMemcpyDeviceToHost, s));
+    B2_CHECK(ctx, cudaStreamSynchronize(s));
+    uint64_t ok = got ? 1 : 0;
+    const cudaIpcMemHandle_t zero = {};
+    for (int r = 0; r < W && ok; r++) {
+        if (r == ctx->rank) continue;
+        if (memcmp(&all[r], &zero, 64) == 0 ||
+            cudaIpcOpenMemHandle(&ctx->x_peer[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            cudaGetLastError();
+            ctx->x_peer[r] = nullptr;
+            ok = 0;
+        }
+    }
+    // all ranks or none: a rank that could not map everything makes everybody use the all-gather
+    B2_CHECK(ctx, cudaMemcpyAsync(d_h, &ok, 8, cudaMemcpyHostToDevice, s));
+    NCCL_TRY(ctx, g_nccl.allreduce(d_h, d_h, 1, NCCL_UINT64, NCCL_SUM, ctx->comm, s));
+    uint64_t n_ok = 0;
+    B2_CHECK(ctx, cudaMemcpyAsync(&n_ok, d_h, 8, cudaMemcpyDeviceToHost, s));
+    B2_CHECK(ctx, cudaStreamSynchronize(s));
+    b2_free(d_h);
+    if (n_ok == (uint64_t)W) ctx->peers_open = true;
+    else { b2_close_peers(ctx); ctx->peers_failed = true; }
+    return 0;
+}
+
+void b2_close_peers(b200spmv_ctx *ctx)
+{
+    for (int r = 0; r < 64; r++)
+        if (ctx->x_peer[r]) { cudaIpcCloseMemHandle(ctx->x_peer[r]); ctx->x_peer[r] = nullptr; }
+    ctx->peers_open = false;
+    ctx->peers_failed = false;
+}
+
 extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_current_x, int flags,
                                       float *ms_total, double *last_norm)
 {
@@ -280,31 +334,57 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
     const int spmv_flags = flags & ~B200SPMV_ACCUMULATE;  // y = A*x each step
     uint64_t *yb = (uint64_t *)ctx->d_y + ctx->row_begin;
     uint64_t *xb = (uint64_t *)ctx->d_x + ctx->row_begin;
-    // Overlap of the exchange with the next step (setup option own_slabs): the slabs that cover this rank's own
-    // block of x only gather what scale_into_x has just written, so they run on the compute stream while the
-    // all-gather of the other blocks is still in flight on a second, higher-priority stream; the remaining slabs
-    // wait for its event.  Strict order keeps the slabs in column order and therefore does not overlap.
+    // Overlap of the exchange with the next step (setup option own_slabs).  The slabs that cover this rank's own
+    // block of x only gather what scale_into_x has just written, so they run on the compute stream while the other
+    // blocks are still on the wire.  exchange 1: one NCCL all-gather on a second, higher-priority stream, the other
+    // slabs wait for its event.  exchange 2: the blocks are pulled one by one out of the peers' x over NVLink by
+    // the copy engines (CUDA IPC mappings; a one-word all-reduce tells that every rank has written its block),
+    // starting with the right-hand neighbour's, and the slabs of a block start as soon as that block has landed.
+    // Strict order keeps the slabs in column order and therefore does not overlap.
     const bool overlap = ctx->world > 1 && ctx->own_hi > ctx->own_lo && !(flags & B200SPMV_STRICT_ORDER);
+    const int W = ctx->world, per_block = ctx->own_hi - ctx->own_lo;
     if (overlap && !ctx->comm_stream) {
         int lo = 0, hi = 0;
         B2_CHECK(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
         B2_CHECK(ctx, cudaStreamCreateWithPriority(&ctx->comm_stream, cudaStreamNonBlocking, hi));
+        for (int i = 0; i < 4; i++) B2_CHECK(ctx, cudaStreamCreateWithPriority(&ctx->pull_stream[i], cudaStreamNonBlocking, hi));
         B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_xready, cudaEventDisableTiming));
         B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_xdone, cudaEventDisableTiming));
+        B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_bar, cudaEventDisableTiming));
+        for (int r = 0; r < W; r++) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_blk[r], cudaEventDisableTiming));
     }
+    int mode = overlap ? ctx->opt_exchange : 0;
+    if (mode == 2) { B2_TRY(open_peers(ctx)); if (!ctx->peers_open) mode = 1; }
+    ctx->exchange_mode = mode;
     cudaStream_t xs = overlap ? ctx->comm_stream : s;
+    if (overlap) {  // own block first, then the blocks of ranks rank+1, rank+2, ... (the order the pulls are issued in)
+        int pos = 0;
+        for (int k = 0; k < W; k++) {
+            const int r = (ctx->rank + k) % W;
+            for (int j = 0; j < per_block; j++) ctx->h_order[pos++] = r * per_block + j;
+        }
+    }
+    uint64_t *barrier_word = (uint64_t *)(ctx->d_norm + 4);
     bool in_flight = false;
     B2_CHECK(ctx, cudaEventRecord(ctx->ev0, s));
     for (int it = 0; it < steps; it++) {
-        ctx->ev_rest = in_flight ? ctx->ev_xdone : nullptr;
+        if (overlap) {
+            for (int pos = 0; pos < ctx->slabs; pos++) ctx->slab_wait[pos] = nullptr;
+            if (in_flight && mode == 1) ctx->slab_wait[per_block] = ctx->ev_xdone;
+            if (in_flight && mode == 2)
+                for (int k = 1; k < W; k++) ctx->slab_wait[k * per_block] = ctx->ev_blk[(ctx->rank + k) % W];
+            ctx->order_n = ctx->slabs;
+        }
         const int rc = b2_spmv_launch(ctx, spmv_flags, s);
-        ctx->ev_rest = nullptr;
+        ctx->order_n = 0;
         if (rc) return rc;
         if (!is_u64) {
             sumsq_partial_kernel<<<RED_BLOCKS, RED_THREADS, 0, s>>>((const double *)yb, ctx->local_rows, partial);
             sumsq_final_kernel<<<1, RED_THREADS, 0, s>>>(partial, RED_BLOCKS, norm2);
             if (ctx->world > 1) NCCL_TRY(ctx, g_nccl.allreduce(norm2, norm2, 1, NCCL_FLOAT64, NCCL_SUM, ctx->comm, s));
         }
+        // peer pulls, u64 (no norm to agree on): nobody overwrites its block before everybody has pulled it
+        if (mode == 2 && is_u64) NCCL_TRY(ctx, g_nccl.allreduce(barrier_word + 1, barrier_word + 1, 1, NCCL_UINT64, NCCL_SUM, ctx->comm, s));
         scale_into_x_kernel<<<ctx->sms * 8, 256, 0, s>>>(yb, ctx->local_rows, norm2, is_u64, xb);
         ctx->launches += is_u64 ? 1 : 3;
         const bool timed = it == steps - 1 && ctx->world > 1;  // exchange time of the last step -> stat "xchgtime_ns"
@@ -316,7 +396,26 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
             if (!ctx->ev_x0) { B2_CHECK(ctx, cudaEventCreate(&ctx->ev_x0)); B2_CHECK(ctx, cudaEventCreate(&ctx->ev_x1)); }
             B2_CHECK(ctx, cudaEventRecord(ctx->ev_x0, xs));
         }
-        B2_TRY(allgather_x(ctx, xs));
+        if (mode == 2) {
+            // every rank's block is written once this all-reduce has gone round; the next step's norm all-reduce
+            // (after every rank's last slab, hence after its pulls) is what lets a rank overwrite its block again
+            NCCL_TRY(ctx, g_nccl.allreduce(barrier_word, barrier_word, 1, NCCL_UINT64, NCCL_SUM, ctx->comm, xs));
+            B2_CHECK(ctx, cudaEventRecord(ctx->ev_bar, xs));
+            const int ns = ctx->opt_pull_streams;
+            for (int i = 0; i < ns; i++) B2_CHECK(ctx, cudaStreamWaitEvent(ctx->pull_stream[i], ctx->ev_bar, 0));
+            for (int k = 1; k < W; k++) {
+                const int r = (ctx->rank + k) % W;
+                const size_t b = ctx->h_row_splits[r], e = ctx->h_row_splits[r + 1];
+                cudaStream_t ps = ctx->pull_stream[(k - 1) % ns];
+                if (e > b)
+                    B2_CHECK(ctx, cudaMemcpyAsync((uint64_t *)ctx->d_x + b, (const uint64_t *)ctx->x_peer[r] + b, (e - b) * 8,
+                                                  cudaMemcpyDefault, ps));
+                B2_CHECK(ctx, cudaEventRecord(ctx->ev_blk[r], ps));
+                B2_CHECK(ctx, cudaStreamWaitEvent(xs, ctx->ev_blk[r], 0));
+            }
+        } else {
+            B2_TRY(allgather_x(ctx, xs));
+        }
         if (timed) B2_CHECK(ctx, cudaEventRecord(ctx->ev_x1, xs));
         if (overlap) {
             B2_CHECK(ctx, cudaEventRecord(ctx->ev_xdone, xs));

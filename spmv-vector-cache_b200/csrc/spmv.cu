@@ -1072,18 +1072,11 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
     const size_t stride = ctx->rowptr_stride;
     const uint32_t rows = ctx->local_rows;
     if (rows == 0) return 0;
-    // slab order: this rank's own block of x first when the caller overlaps the exchange of the other blocks
-    const int n_own = ctx->ev_rest ? ctx->own_hi - ctx->own_lo : 0;
+    // slab order: column order, unless the iterated SpMV has put this rank's own block of x first (common.cuh)
+    const bool ordered = ctx->order_n == ctx->slabs;
     for (int pos = 0; pos < ctx->slabs; pos++) {
-        int sl = pos;
-        if (n_own > 0) {
-            if (pos < n_own) sl = ctx->own_lo + pos;
-            else {
-                sl = pos - n_own;
-                if (sl >= ctx->own_lo) sl += n_own;
-                if (pos == n_own) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_rest, 0));
-            }
-        }
+        const int sl = ordered ? ctx->h_order[pos] : pos;
+        if (ordered && ctx->slab_wait[pos]) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->slab_wait[pos], 0));
         const uint32_t *rowptr = m.rowptr + sl * stride;
         const bool read_y = accumulate || pos > 0;
         if (ctx->wait_slab_events) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_slab[sl], 0));

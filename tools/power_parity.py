@@ -1,10 +1,10 @@
 #!/usr/bin/env python
 """Iterated SpMV over several GPUs against the same iteration on one GPU (run under torchrun, >= 2 ranks).
 
-Every rank builds (a) its row block of a banded+random matrix with the slabs aligned to the ranks' x blocks, so
-that b200spmv_power_iterate overlaps the all-gather of x with the slabs of its own block, (b) the same block
-without the overlap, (c) the whole matrix alone.  After K steps the replicated x of (a) and (b) must equal the x
-of (c): bit for bit for uint64, to 1e-12 relative for fp64 (the slabs are summed in another order).
+Every rank builds its row block of a banded+random matrix (a) with the slabs aligned to the ranks' x blocks and
+the other blocks pulled from the peers block by block under the slabs (exchange 2), (b) the same with one NCCL
+all-gather under the own-block slabs (exchange 1), (c) with the all-gather after the step, and (d) the whole matrix
+alone.  After K steps the replicated x of (a)-(c) must equal the x of (d): bit for bit for uint64, to 1e-12 relative for fp64 (the slabs are summed in another order).
 """
 import importlib.util
 import os
@@ -20,7 +20,7 @@ b2 = importlib.util.module_from_spec(spec)
 spec.loader.exec_module(b2)
 
 
-def make(local, rank, world, dtype, rows, npr, slabs, own):
+def make(local, rank, world, dtype, rows, npr, slabs, own, exchange=2):
     e = b2.Engine(local)
     if world > 1:
         uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -30,6 +30,7 @@ def make(local, rank, world, dtype, rows, npr, slabs, own):
         e.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
         if own:
             e.set_option("own_slabs", 1)
+            e.set_option("exchange", exchange)
     if slabs:
         e.set_option("slabs", slabs)
     e.setup_synthetic(2, rows, rows, npr, 12345, dtype)
@@ -41,17 +42,21 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     bad = 0
+    quick = "quick" in sys.argv[1:]  # one unequal-block case and one large one (8-GPU runs are charged 8x)
+    cases = (((1 << 20) + 8 * 977, 3), (1 << 22, 0)) if quick else ((1 << 20, 0), (1 << 20, 4), ((1 << 20) + 8 * 977, 3), (1 << 22, 0))
     for dtype, name in ((b2.F64, "f64"), (b2.U64, "u64")):
-        for rows, slabs in ((1 << 20, 0), (1 << 20, 4), ((1 << 20) + 8 * 977, 3), (1 << 22, 0)):
+        for rows, slabs in cases:
             steps = 6 if dtype == b2.F64 else 3
             single = make(local, 0, 1, dtype, rows, 5, slabs, False)
             single.power_iterate(steps, False, 0)
             want = single.get_x()
             del single
-            for own in (True, False):
-                e = make(local, rank, world, dtype, rows, 5, slabs, own)
-                _, nrm = e.power_iterate(steps, False, 0)
-                # a second call continues from the replicated x (what bench.py does after its warm-up)
+            for own, exchange in ((True, 2),) if quick else ((True, 2), (True, 1), (False, 0)):
+                e = make(local, rank, world, dtype, rows, 5, slabs, own, exchange)
+                # two calls: the second continues from the replicated x (what bench.py does after its warm-up)
+                e.power_iterate(steps // 2, False, 0)
+                e.power_iterate(steps - steps // 2, True, 0)
+                assert e.stat("exchange_mode") == exchange, e.stat("exchange_mode")
                 got = e.get_x()
                 if dtype == b2.U64:
                     ok = np.array_equal(got, want)
@@ -59,8 +64,8 @@ def main():
                 else:
                     err = float(np.max(np.abs(got - want)) / np.max(np.abs(want)))
                     ok = err < 1e-12
-                print("rank %d %s rows %d slabs opt %d -> %d own_slabs %d: %s (%s)" %
-                      (rank, name, rows, slabs, e.stat("slabs"), own, "ok" if ok else "MISMATCH", err), flush=True)
+                print("rank %d %s rows %d slabs opt %d -> %d exchange %d: %s (%s)" %
+                      (rank, name, rows, slabs, e.stat("slabs"), exchange, "ok" if ok else "MISMATCH", err), flush=True)
                 bad += not ok
                 del e
     t = torch.tensor([bad], device="cuda")
