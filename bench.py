@@ -219,6 +219,10 @@ def run_ours(args):
         eng.set_option("prefetch_tiles", args.prefetch)
     if args.graph is not None:
         eng.set_option("graph", args.graph)
+    if args.own_slabs:
+        eng.set_option("own_slabs", 1)
+    if args.prefetch_x is not None:
+        eng.set_option("prefetch_x", args.prefetch_x)
     if args.workload == "banded-power" and world > 1 and not args.shard and args.exchange != "nccl":
         # slabs aligned with the ranks' x blocks: the exchange of the other blocks runs under the own-block slabs
         eng.set_option("own_slabs", 1)
@@ -270,8 +274,10 @@ def run_ours(args):
     eng.set_option("profile", 1)
     eng.exec_device(args.steps, flags)
     k_ns, k_n = eng.stat("merge_kernel_ns"), eng.stat("merge_kernel_launches")
-    eng.set_option("profile", 0)
     slabs = eng.stat("slabs")
+    per_slab = [{"ms": round(eng.stat("slab_ns_%d" % i) * 1e-6 / args.steps, 4), "nnz": eng.stat("slab_nnz_%d" % i),
+                 "nonempty_rows": eng.stat("slab_rows_%d" % i), "longest_row": eng.stat("slab_maxrow_%d" % i)} for i in range(slabs)] if args.per_slab else None
+    eng.set_option("profile", 0)
     eng_mode = eng.stat("mode")
     traffic, traffic_src = recorded_traffic(args.workload, rows, cols, slabs, eng_mode, world, flags)
     # the strict kernel has no per-launch bracket: its step time is the kernel time (one launch per slab)
@@ -313,7 +319,8 @@ def run_ours(args):
                        **({"x_exchange_ms_last_step": eng.stat("xchgtime_ns") * 1e-6, "exchange": ["NCCL all-gather after the step", "NCCL all-gather under the own-block slabs",
                                         "peer pulls block by block under the slabs"][eng.stat("exchange_mode")]}
                           if power and world > 1 else {}),
-                       **({"norm_after_last_step": last_norm} if power else {})},
+                       **({"norm_after_last_step": last_norm} if power else {}),
+                       **({"per_slab": per_slab} if per_slab else {})},
             "gb_s_algorithmic": b_alg(nnz, rows, cols) * args.steps / t_dev / 1e9 if world == 1 else None,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
@@ -359,6 +366,9 @@ def main():
     ap.add_argument("--exchange", choices=["pull", "overlap", "nccl"], default="pull",
                     help="power iteration over several GPUs: how the replicated x is refreshed (DESIGN.md section 7)")
     ap.add_argument("--pull-streams", type=int, default=0)
+    ap.add_argument("--prefetch-x", type=int, default=None, help="1: bulk-prefetch each slab's x slice into L2 before its kernel")
+    ap.add_argument("--own-slabs", action="store_true", help="with --shard: cut the slabs along the ranks' x blocks")
+    ap.add_argument("--per-slab", action="store_true", help="add the kernel time of every slab to config")
     ap.add_argument("--strict", action="store_true", help="strict-order kernel (fp64 memcmp-equal to SoftwareSpMV)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

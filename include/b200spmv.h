@@ -68,7 +68,14 @@ B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx ma
  * "keep_csc" (1 = keep the device CSC copy for b200spmv_get_csc), "profile", "kernel" (1..5, see
  * DESIGN.md 3.2; default 3), "ept", "ctas_per_sm" (kernel tuning), "world" then "rank" (take the
  * place of rank r of w in the nnz-balanced row-block split WITHOUT a communicator: a single SpMV
- * needs no collective; b200spmv_power_iterate does and refuses). */
+ * needs no collective; b200spmv_power_iterate does and refuses).
+ * For iterated SpMV over several ranks: "own_slabs" (1 = cut the column slabs along the ranks' blocks of
+ * x, so that b200spmv_power_iterate can run the slabs of a rank's own block while the other blocks are
+ * still on the wire), "exchange" (with own_slabs: 2 = the other blocks are pulled from the peers' x over
+ * NVLink by the copy engines through CUDA IPC mappings, block by block, each block's slabs starting when
+ * it has landed -- the default, falls back to 1 where peers cannot be mapped; 1 = one NCCL all-gather under
+ * the own-block slabs), "pull_streams" (copy streams of exchange 2, default 2).  Stat "exchange_mode"
+ * reports what the last b200spmv_power_iterate did (0 = NCCL all-gather after the step). */
 B200SPMV_API int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t value);
 
 /* ---- setup: upload CSC, transpose to CSR on the device (once, amortised) ------------- */

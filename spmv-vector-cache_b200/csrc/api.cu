@@ -102,6 +102,8 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "dcsr_x16") ctx->opt_dcsr_x16 = (int)value;
     else if (k == "prefetch_tiles") ctx->opt_prefetch_tiles = (int)std::max<int64_t>(0, value);
     else if (k == "graph") ctx->opt_graph = (int)value;
+    else if (k == "prefetch_x") ctx->opt_prefetch_x = (int)value;
+    else if (k == "dcsr_maxrow") ctx->opt_dcsr_maxrow = (int)value;
     else if (k == "exchange") { if (value < 1 || value > 2) return b2_fail(ctx, B200SPMV_EINVAL, "exchange must be 1 or 2"); ctx->opt_exchange = (int)value; }
     else if (k == "pull_streams") { if (value < 1 || value > 4) return b2_fail(ctx, B200SPMV_EINVAL, "pull_streams must be 1..4"); ctx->opt_pull_streams = (int)value; }
     else if (k == "own_slabs") {
@@ -117,7 +119,7 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
         if (k == "world") { if (value < 1 || value > 64) return b2_fail(ctx, B200SPMV_EINVAL, "world must be 1..64"); ctx->world = (int)value; if (ctx->rank >= ctx->world) ctx->rank = 0; }
         else { if (value < 0 || value >= ctx->world) return b2_fail(ctx, B200SPMV_EINVAL, "rank must be 0..world-1"); ctx->rank = (int)value; }
     }
-    else if (k == "profile") { ctx->opt_profile = (int)value; ctx->merge_kernel_ns = 0; ctx->merge_kernel_launches = 0; ctx->prof_n = 0; }
+    else if (k == "profile") { ctx->opt_profile = (int)value; ctx->merge_kernel_ns = 0; ctx->merge_kernel_launches = 0; ctx->prof_n = 0; memset(ctx->prof_slab_ns, 0, sizeof ctx->prof_slab_ns); }
     else return b2_fail(ctx, B200SPMV_EINVAL, "unknown option");
     return 0;
 }
@@ -134,8 +136,13 @@ static int choose_slabs(const b200spmv_ctx *ctx)
     // work on.  When an L2-sized slab would hold only a few entries per row (C5: 16 entries per row over 18
     // slabs; C4: 32 over 9) that costs more than the L2 hits save: keep >= 8 entries per row and slab and
     // let part of the gathers go to HBM (profiles/r01_c5_shard_sweep.txt, r01_c4_shard_sweep.txt).
-    const double per_row = ctx->local_rows ? (double)ctx->local_nnz / (double)ctx->local_rows : 0.0;
-    s = std::max(1, std::min(s, (int)(per_row / 8.0)));
+    // (per NON-EMPTY row: the empty rows of a skewed block cost the kernels nothing; profiles/r01_c4_shard_sweep.txt)
+    const double per_row = ctx->nonempty_rows ? (double)ctx->local_nnz / (double)ctx->nonempty_rows : 0.0;
+    int by_rows = (int)(per_row / 8.0);
+    // Column skew (R-MAT: 3/4 of the entries sit in the lower half of the columns): most of the uniform slabs
+    // then hold far fewer entries per row than the average says, so fewer of them pay off.
+    if (ctx->upper_half_nnz * 100 < ctx->local_nnz * 35) by_rows = (by_rows * 2 + 2) / 3;
+    s = std::max(1, std::min(s, by_rows));
     return s;
 }
 
@@ -145,6 +152,14 @@ static int csc_to_csr(b200spmv_ctx *ctx, uint32_t index_mask)
     cudaStream_t s = ctx->stream;
     DeviceCsr &m = ctx->csr;
     const uint64_t t0 = now_ns();
+    B2_TRY(b2_count_nonempty(ctx, ctx->local_rows, ctx->local_nnz, ctx->csc_rowind, index_mask, ctx->row_begin,
+                             &ctx->nonempty_rows, s));
+    {
+        uint32_t mid = 0;
+        B2_CHECK(ctx, cudaMemcpyAsync(&mid, ctx->csc_colptr + ctx->cols / 2, 4, cudaMemcpyDeviceToHost, s));
+        B2_CHECK(ctx, cudaStreamSynchronize(s));
+        ctx->upper_half_nnz = ctx->local_nnz - mid;
+    }
     ctx->slabs = choose_slabs(ctx);
     ctx->own_lo = ctx->own_hi = 0;
     bool own = ctx->opt_own_slabs && ctx->world > 1 && ctx->rows == ctx->cols && ctx->h_row_splits;
@@ -510,7 +525,14 @@ extern "C" int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *o
     else if (k == "setuptime_ns") *out = ctx->setuptime_ns;
     else if (k == "transposetime_ns") *out = ctx->transposetime_ns;
     else if (k == "xchgtime_ns") *out = ctx->xchgtime_ns;
+    else if (k == "nonempty_rows") *out = ctx->nonempty_rows;
     else if (k == "exchange_mode") *out = (uint64_t)ctx->exchange_mode;
+    else if (k.rfind("slab_ns_", 0) == 0 || k.rfind("slab_nnz_", 0) == 0 || k.rfind("slab_rows_", 0) == 0 || k.rfind("slab_maxrow_", 0) == 0) {
+        const int i = atoi(k.c_str() + k.rfind('_') + 1);
+        if (i < 0 || i >= ctx->slabs) return b2_fail(ctx, B200SPMV_EINVAL, "no such slab");
+        *out = k[5] == 'n' && k[6] == 's' ? ctx->prof_slab_ns[i] : k[5] == 'n' ? (uint64_t)ctx->h_slab_nnz[i]
+               : k[5] == 'm' ? (uint64_t)ctx->h_maxrow[i] : (uint64_t)ctx->h_nseg[i];
+    }
     else if (k == "slabs") *out = (uint64_t)ctx->slabs;
     else if (k == "l2_persist_bytes") *out = ctx->max_persist_bytes;
     else if (k == "l2_bytes") *out = ctx->l2_bytes;

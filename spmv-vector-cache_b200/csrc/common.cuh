@@ -61,6 +61,8 @@ struct b200spmv_ctx {
     int opt_own_slabs = 0;        // 1: align the slabs with the ranks' blocks of x (set before setup; see own_lo)
     int opt_exchange = 2;         // with own_slabs: 1 = NCCL all-gather under the own-block slabs, 2 = peer pulls
     int opt_pull_streams = 2;     // copy streams the peer pulls are spread over
+    int opt_dcsr_maxrow = 64;     // ... and only when no row piece of the slab is longer than this
+    int opt_prefetch_x = 0;       // 1: stream each slab's slice of x into L2 (UBLKPF) before its kernel
     int opt_graph = 1;            // b200spmv_exec_device replays a captured CUDA graph of one step
     int opt_ablate = 0;           // kernel 5 only, measurement: see spmv_flag_warp_kernel
     int opt_ctas_per_sm = 4;      // persistent grid of kernel 4 = sms * this
@@ -76,6 +78,8 @@ struct b200spmv_ctx {
     uint32_t local_rows = 0;
     size_t rowptr_stride = 0;     // elements between the slabs' row-pointer arrays (multiple of 4)
     uint64_t local_nnz = 0;
+    uint64_t nonempty_rows = 0;   // of this rank's block
+    uint64_t upper_half_nnz = 0;  // entries of the block in columns >= cols/2 (column skew, choose_slabs)
     int slabs = 1;
     uint32_t slab_cols = 0;       // columns per slab (last may be short) when the slabs are uniform
     uint32_t h_slab_col[65] = {0};     // column boundaries of the slabs
@@ -99,6 +103,7 @@ struct b200spmv_ctx {
     uint64_t h_slab_off[65] = {0};     // entry offset of each slab in colind/vals (padded to FLAG_TILE)
     uint32_t h_slab_nnz[64] = {0};
     uint32_t h_nseg[64] = {0};         // non-empty rows per slab
+    uint32_t h_maxrow[64] = {0};       // longest row piece per slab
     bool flagged = false;              // colind carries row-start flags in bit 31
     uint32_t colmask = 0xFFFFFFFFu;    // mask that strips the flag
     uint64_t padded_nnz = 0;
@@ -134,6 +139,7 @@ struct b200spmv_ctx {
     cudaEvent_t prof_ev[128] = {nullptr};
     int prof_n = 0;               // events recorded since the last read
     uint64_t merge_kernel_ns = 0, merge_kernel_launches = 0;
+    uint64_t prof_slab_ns[64] = {0};  // the same, by position of the launch within a step
     int last_mode = 0;
 };
 
@@ -199,6 +205,8 @@ int b2_compress(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *k
                 const uint32_t *src_other, const void *src_vals, uint32_t *dst_ptr, uint32_t dst_ptr_add,
                 uint32_t *dst_ind, void *dst_vals, cudaStream_t s);
 int b2_add_u32(b200spmv_ctx *ctx, uint32_t *a, uint64_t n, uint32_t add, cudaStream_t s);
+int b2_count_nonempty(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *key, uint32_t key_mask,
+                      uint32_t key_sub, uint64_t *out, cudaStream_t s);
 // spmv.cu
 int b2_build_tiles(b200spmv_ctx *ctx);
 int b2_build_flags(b200spmv_ctx *ctx);

@@ -982,6 +982,16 @@ int b2_build_tiles(b200spmv_ctx *ctx)
 }
 
 // Flagged format for kernel 3 (needs bit 31 of the column ids free).
+// longest row piece of a slab: the thread-per-row kernel is only chosen when no thread gets a long one
+__global__ void max_rowlen_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, uint32_t *__restrict__ out)
+{
+    uint32_t v = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += (uint64_t)gridDim.x * blockDim.x)
+        v = max(v, rowptr[i + 1] - rowptr[i]);
+    v = __reduce_max_sync(0xFFFFFFFFu, v);
+    if ((threadIdx.x & 31) == 0 && v > 0) atomicMax(out, v);
+}
+
 int b2_build_flags(b200spmv_ctx *ctx)
 {
     DeviceCsr &m = ctx->csr;
@@ -1024,6 +1034,10 @@ int b2_build_flags(b200spmv_ctx *ctx)
             rowptr, segidx, rows, (uint32_t)ctx->h_slab_off[sl], nt * WK_PER_TILE, WK_ENTRIES,
             m.warp_seg + (size_t)ctx->h_ftile_base[sl] * WK_PER_TILE + sl);
         cudaError_t e = cudaMemcpyAsync(&ctx->h_nseg[sl], segidx + rows, 4, cudaMemcpyDeviceToHost, s);
+        // segidx[rows + 1] is free after the scan: scratch word for the longest row piece
+        if (e == cudaSuccess) e = cudaMemsetAsync(segidx + rows + 1, 0, 4, s);
+        max_rowlen_kernel<<<ctx->sms * 8, 256, 0, s>>>(rowptr, rows, segidx + rows + 1);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&ctx->h_maxrow[sl], segidx + rows + 1, 4, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess) e = cudaStreamSynchronize(s);
         if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; rc = B200SPMV_ECUDA; }
     }
@@ -1059,6 +1073,19 @@ static int set_persist_window(b200spmv_ctx *ctx, cudaStream_t s, const void *bas
     return 0;
 }
 
+// The slab's slice of x, streamed into L2 by the TMA unit ahead of the gathers (cp.async.bulk.prefetch.L2 ->
+// UBLKPF, nothing returns to the SM): the first gather of every sector is then an L2 hit instead of a random
+// 32-byte DRAM read (42-65 G/s, profiles/r01_gather_paths.txt).  One 16 KB request per thread.
+constexpr uint32_t XPF_CHUNK = 16384;
+__global__ void x_prefetch_kernel(const char *base, uint64_t bytes)
+{
+    const uint64_t off = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * XPF_CHUNK;
+    if (off < bytes) {
+        const uint32_t n = (uint32_t)min((uint64_t)XPF_CHUNK, bytes - off);
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(base + off), "r"(n) : "memory");
+    }
+}
+
 template <int DT>
 static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
 {
@@ -1079,6 +1106,15 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
         if (ordered && ctx->slab_wait[pos]) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->slab_wait[pos], 0));
         const uint32_t *rowptr = m.rowptr + sl * stride;
         const bool read_y = accumulate || pos > 0;
+        if (ctx->opt_prefetch_x && ctx->slabs > 1) {
+            // whole 16-byte units around the slice (every device array is padded by 256 bytes)
+            const uint64_t b0 = (uint64_t)ctx->h_slab_col[sl] * 8 & ~15ull, b1 = ((uint64_t)ctx->h_slab_col[sl + 1] * 8 + 15) & ~15ull;
+            if (b1 > b0 && (double)(b1 - b0) <= 0.6 * (double)ctx->l2_bytes) {
+                const uint64_t nthr = (b1 - b0 + XPF_CHUNK - 1) / XPF_CHUNK;
+                x_prefetch_kernel<<<(unsigned)((nthr + 127) / 128), 128, 0, s>>>((const char *)x + b0, b1 - b0);
+                ctx->launches += 1;
+            }
+        }
         if (ctx->wait_slab_events) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_slab[sl], 0));
         if (!strict && ctx->opt_kernel >= 3 && ctx->flagged) {
             const uint32_t tb = ctx->h_ftile_base[sl];
@@ -1095,9 +1131,11 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
                 if (!ctx->prof_ev[ctx->prof_n]) { cudaEventCreate(&ctx->prof_ev[ctx->prof_n]); cudaEventCreate(&ctx->prof_ev[ctx->prof_n + 1]); }
                 cudaEventRecord(ctx->prof_ev[ctx->prof_n], s);
             }
-            // hypersparse slab (fewer than opt_dcsr_x16/16 entries per non-empty row): thread per non-empty row
+            // hypersparse slab (fewer than opt_dcsr_x16/16 entries per non-empty row and no long row: on a skewed
+            // matrix one thread with a few thousand entries holds the whole launch up): thread per non-empty row
             const uint32_t nseg = ctx->h_nseg[sl];
-            if (ctx->opt_dcsr_x16 > 0 && nseg > 0 && (uint64_t)ctx->h_slab_nnz[sl] * 16 < (uint64_t)nseg * ctx->opt_dcsr_x16) {
+            if (ctx->opt_dcsr_x16 > 0 && nseg > 0 && (uint64_t)ctx->h_slab_nnz[sl] * 16 < (uint64_t)nseg * ctx->opt_dcsr_x16 &&
+                ctx->h_maxrow[sl] <= (uint32_t)ctx->opt_dcsr_maxrow) {
                 const unsigned grid = b2_div_up(nseg, 256);
                 if (persist) {
                     if (read_y) spmv_dcsr_kernel<DT, true, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
@@ -1220,6 +1258,7 @@ void b2_profile_collect(b200spmv_ctx *ctx)
         if (cudaEventElapsedTime(&ms, ctx->prof_ev[i], ctx->prof_ev[i + 1]) == cudaSuccess) {
             ctx->merge_kernel_ns += (uint64_t)((double)ms * 1e6);
             ctx->merge_kernel_launches++;
+            ctx->prof_slab_ns[(i / 2) % ctx->slabs] += (uint64_t)((double)ms * 1e6);  // collected at step boundaries
         }
     }
     ctx->prof_n = 0;

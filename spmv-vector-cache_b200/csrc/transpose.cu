@@ -54,6 +54,48 @@ __global__ void add_u32_kernel(uint32_t *__restrict__ a, uint64_t n, uint32_t ad
 
 }  // namespace
 
+// rows that hold at least one of the n entries (bitmap + popcount); the slab heuristic counts entries per
+// NON-EMPTY row: the empty rows of a skewed matrix cost the kernels nothing
+__global__ void mark_rows_kernel(const uint32_t *__restrict__ key, uint32_t key_mask, uint32_t key_sub, uint64_t n,
+                                 uint32_t *__restrict__ bitmap)
+{
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t r = (key[e] & key_mask) - key_sub, bit = 1u << (r & 31);
+        if (!(bitmap[r >> 5] & bit)) atomicOr(bitmap + (r >> 5), bit);  // the plain read keeps hub rows off the atomic unit
+    }
+}
+__global__ void popcount_kernel(const uint32_t *__restrict__ bitmap, uint64_t words, unsigned long long *__restrict__ out)
+{
+    unsigned c = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (uint64_t)gridDim.x * blockDim.x)
+        c += __popc(bitmap[i]);
+    c = __reduce_add_sync(0xFFFFFFFFu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
+}
+
+int b2_count_nonempty(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *key, uint32_t key_mask,
+                      uint32_t key_sub, uint64_t *out, cudaStream_t s)
+{
+    *out = 0;
+    if (n == 0 || nkeys == 0) return 0;
+    const uint64_t words = ((uint64_t)nkeys + 31) / 32;
+    uint32_t *bm = nullptr;
+    B2_TRY(b2_alloc(ctx, &bm, words + 2));  // the counter sits behind the bitmap, 8-byte aligned
+    unsigned long long *cnt = (unsigned long long *)(bm + ((words + 1) & ~1ull));
+    int rc = 0;
+    cudaError_t e = cudaMemsetAsync(bm, 0, (words + 4) * 4, s);
+    const unsigned grid = (unsigned)std::min<uint64_t>(b2_div_up(n, 256), (uint64_t)ctx->sms * 32);
+    mark_rows_kernel<<<grid, 256, 0, s>>>(key, key_mask, key_sub, n, bm);
+    popcount_kernel<<<(unsigned)std::min<uint64_t>(b2_div_up(words, 256), (uint64_t)ctx->sms * 8), 256, 0, s>>>(bm, words, cnt);
+    unsigned long long h = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&h, cnt, 8, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; rc = B200SPMV_ECUDA; }
+    b2_free(bm);
+    *out = h;
+    return rc;
+}
+
 int b2_add_u32(b200spmv_ctx *ctx, uint32_t *a, uint64_t n, uint32_t add, cudaStream_t s)
 {
     if (n == 0 || add == 0) return 0;
