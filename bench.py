@@ -300,6 +300,7 @@ def run_ours(args):
         eng.exec(xh.data_ptr(), yh.data_ptr(), flags)  # H2D x (+y), kernels, D2H y; blocking
     torch.cuda.synchronize()
     t_e2e = max_over_ranks(time.perf_counter() - t0)
+    timeline = {k: round(eng.stat("exec_%s_ns" % k) * 1e-6, 3) for k in ("x_up", "y_up", "kernels", "done")}
     barrier()
     clocks = sampler.stop()
     h2d = 8 * cols + (8 * lrows if flags & b2.ACCUMULATE else 0)
@@ -329,7 +330,8 @@ def run_ours(args):
                          "kernel_launches_per_step": slabs,
                          "algorithmic_bytes_per_step": alg_local, "frac_of_8TBs_nominal": achieved / 8000.0},
             "e2e": {"value": nnz * e2e_steps / t_e2e / 1e9, "unit": "GNNZ/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": 1e3 * t_e2e / e2e_steps},
+                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": 1e3 * t_e2e / e2e_steps,
+                    "last_step_timeline_ms": timeline},
             "gpu_launches": int(launches), "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:

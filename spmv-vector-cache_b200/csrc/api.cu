@@ -79,6 +79,8 @@ extern "C" void b200spmv_destroy(b200spmv_ctx *ctx)
     if (ctx->ev_x0) { cudaEventDestroy(ctx->ev_x0); cudaEventDestroy(ctx->ev_x1); }
     if (ctx->comm_stream) { cudaStreamDestroy(ctx->comm_stream); cudaEventDestroy(ctx->ev_xready); cudaEventDestroy(ctx->ev_xdone); cudaEventDestroy(ctx->ev_bar); }
     for (int i = 0; i < 4; i++) if (ctx->pull_stream[i]) cudaStreamDestroy(ctx->pull_stream[i]);
+    if (ctx->ev_tl[0]) for (auto &e : ctx->ev_tl) cudaEventDestroy(e);
+    if (ctx->d2h_stream) { cudaStreamDestroy(ctx->d2h_stream); for (int k = 0; k < Y_CHUNKS; k++) cudaEventDestroy(ctx->ev_rowchunk[k]); }
     for (int i = 0; i < 64; i++) if (ctx->ev_blk[i]) cudaEventDestroy(ctx->ev_blk[i]);
     cudaStreamDestroy(ctx->stream); cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
@@ -312,6 +314,9 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
     // x goes up slab slice by slab slice on the copy stream: the kernels of slab s only gather from slice s,
     // so they start as soon as it has landed (b2_spmv_launch waits on ev_slab[s]) while the rest still uploads
     const bool sliced_x = ctx->slabs > 1 && !(flags & B200SPMV_STRICT_ORDER) && (size_t)ctx->cols * 8 >= (8u << 20);
+    if (!ctx->ev_tl[0]) for (auto &e : ctx->ev_tl) B2_CHECK(ctx, cudaEventCreate(&e));
+    B2_CHECK(ctx, cudaEventRecord(ctx->ev_tl[0], ctx->copy_stream));
+    B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_tl[0], 0));
     if (sliced_x) {
         for (int sl = 0; sl < ctx->slabs; sl++) {
             const size_t c0 = ctx->h_slab_col[sl], c1 = ctx->h_slab_col[sl + 1];
@@ -323,17 +328,24 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
     } else {
         B2_CHECK(ctx, cudaMemcpyAsync(ctx->d_x, x_host, (size_t)ctx->cols * 8, cudaMemcpyHostToDevice, s));
     }
+    B2_CHECK(ctx, cudaEventRecord(ctx->ev_tl[1], sliced_x ? ctx->copy_stream : s));
     // Accumulating with the throughput kernels: the upload of the caller's y rides on the copy stream while
     // t = A*x is computed, then y = y_in + t (one more re-association of a sum those kernels re-associate
     // anyway).  Strict order keeps the reference's sequence ((y_in + p1) + p2) ... and uploads y first.
     const bool overlap_y = (flags & B200SPMV_ACCUMULATE) && !(flags & B200SPMV_STRICT_ORDER) && ctx->local_rows > 0 &&
                            ctx->local_rows * 8ull >= (1ull << 20);
+    // Download pipeline: with kernel 3 the last slab is launched in Y_CHUNKS pieces of tiles and the rows a piece
+    // completes go down (and, accumulating, have the caller's y added first) while the later pieces still run.
+    // The row chunks then follow the pieces' boundaries instead of being equal.
+    const bool row_chunks = ctx->local_rows * 8ull >= (1ull << 20) && b2_last_slab_chunkable(ctx, flags);
+    uint64_t cb[Y_CHUNKS + 1];
+    for (int k = 0; k <= Y_CHUNKS; k++) cb[k] = row_chunks ? ctx->h_chunk_row[k] : (uint64_t)ctx->local_rows * k / Y_CHUNKS;
     if (overlap_y) {
         if (!ctx->d_yin) { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->rows)); ctx->d_yin = v; }
         // in Y_CHUNKS row chunks, each with its own event: chunk k is added and sent back (other PCIe
         // direction) while the chunks after it are still on their way up
         for (int k = 0; k < Y_CHUNKS; k++) {
-            const uint64_t r0 = (uint64_t)ctx->local_rows * k / Y_CHUNKS, r1 = (uint64_t)ctx->local_rows * (k + 1) / Y_CHUNKS;
+            const uint64_t r0 = cb[k], r1 = cb[k + 1];
             if (!ctx->ev_ychunk[k]) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_ychunk[k], cudaEventDisableTiming));
             if (r1 > r0)
                 B2_CHECK(ctx, cudaMemcpyAsync((uint64_t *)ctx->d_yin + ctx->row_begin + r0, yh + r0, (size_t)(r1 - r0) * 8,
@@ -343,30 +355,52 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
     } else if (flags & B200SPMV_ACCUMULATE) {
         B2_CHECK(ctx, cudaMemcpyAsync(yd, yh, (size_t)ctx->local_rows * 8, cudaMemcpyHostToDevice, s));
     }
+    B2_CHECK(ctx, cudaEventRecord(ctx->ev_tl[2], overlap_y ? ctx->copy_stream : s));
     B2_CHECK(ctx, cudaEventRecord(ctx->ev0, s));
+    if (row_chunks && !ctx->d2h_stream) {
+        B2_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking));
+        for (int k = 0; k < Y_CHUNKS; k++) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_rowchunk[k], cudaEventDisableTiming));
+    }
     ctx->wait_slab_events = sliced_x;
+    ctx->want_row_chunks = row_chunks;
+    ctx->did_row_chunks = false;
     const int rc_launch = b2_spmv_launch(ctx, overlap_y ? (flags & ~B200SPMV_ACCUMULATE) : flags, s);
     ctx->wait_slab_events = false;
+    ctx->want_row_chunks = false;
     B2_TRY(rc_launch);
     B2_CHECK(ctx, cudaEventRecord(ctx->ev1, s));
-    if (overlap_y) {
-        const uint64_t *yin = (const uint64_t *)ctx->d_yin + ctx->row_begin;
+    const uint64_t *yin = overlap_y ? (const uint64_t *)ctx->d_yin + ctx->row_begin : nullptr;
+    if (overlap_y || ctx->did_row_chunks) {
+        // chunk k: (rows final) -> (caller's y landed, added) -> download; on its own stream when the kernel
+        // pieces are still running on s
+        cudaStream_t ds = ctx->did_row_chunks ? ctx->d2h_stream : s;
         for (int k = 0; k < Y_CHUNKS; k++) {
-            const uint64_t r0 = (uint64_t)ctx->local_rows * k / Y_CHUNKS, r1 = (uint64_t)ctx->local_rows * (k + 1) / Y_CHUNKS;
+            const uint64_t r0 = cb[k], r1 = cb[k + 1];
             if (r1 == r0) continue;
-            B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_ychunk[k], 0));
-            const unsigned grid = (unsigned)std::min<uint64_t>(b2_div_up(r1 - r0, 256), (uint64_t)ctx->sms * 16);
-            if (ctx->dtype == B200SPMV_F64) vec_accumulate_kernel<B200SPMV_F64><<<grid, 256, 0, s>>>(yd + r0, yin + r0, r1 - r0);
-            else vec_accumulate_kernel<B200SPMV_U64><<<grid, 256, 0, s>>>(yd + r0, yin + r0, r1 - r0);
-            B2_CHECK(ctx, cudaGetLastError());
-            ctx->launches += 1;
-            B2_CHECK(ctx, cudaMemcpyAsync(yh + r0, yd + r0, (size_t)(r1 - r0) * 8, cudaMemcpyDeviceToHost, s));
+            if (ctx->did_row_chunks) B2_CHECK(ctx, cudaStreamWaitEvent(ds, ctx->ev_rowchunk[k], 0));
+            if (overlap_y) {
+                B2_CHECK(ctx, cudaStreamWaitEvent(ds, ctx->ev_ychunk[k], 0));
+                const unsigned grid = (unsigned)std::min<uint64_t>(b2_div_up(r1 - r0, 256), (uint64_t)ctx->sms * 16);
+                if (ctx->dtype == B200SPMV_F64) vec_accumulate_kernel<B200SPMV_F64><<<grid, 256, 0, ds>>>(yd + r0, yin + r0, r1 - r0);
+                else vec_accumulate_kernel<B200SPMV_U64><<<grid, 256, 0, ds>>>(yd + r0, yin + r0, r1 - r0);
+                B2_CHECK(ctx, cudaGetLastError());
+                ctx->launches += 1;
+            }
+            B2_CHECK(ctx, cudaMemcpyAsync(yh + r0, yd + r0, (size_t)(r1 - r0) * 8, cudaMemcpyDeviceToHost, ds));
         }
+        B2_CHECK(ctx, cudaEventRecord(ctx->ev_tl[4], ds));
+        if (ctx->did_row_chunks) B2_CHECK(ctx, cudaStreamSynchronize(ds));
     } else {
         B2_CHECK(ctx, cudaMemcpyAsync(yh, yd, (size_t)ctx->local_rows * 8, cudaMemcpyDeviceToHost, s));
+        B2_CHECK(ctx, cudaEventRecord(ctx->ev_tl[4], s));
     }
     B2_CHECK(ctx, cudaStreamSynchronize(s));
+    B2_CHECK(ctx, cudaStreamSynchronize(ctx->copy_stream));
     float ms = 0.f;
+    for (int i = 0; i < 4; i++) {
+        cudaEvent_t e = i == 2 ? ctx->ev1 : ctx->ev_tl[i < 2 ? i + 1 : 4];
+        ctx->tl_ns[i] = cudaEventElapsedTime(&ms, ctx->ev_tl[0], e) == cudaSuccess ? (uint64_t)((double)ms * 1e6) : 0;
+    }
     B2_CHECK(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
     ctx->spmvtime_ns = (uint64_t)((double)ms * 1e6);
     const uint64_t total = now_ns() - t0;
@@ -526,6 +560,10 @@ extern "C" int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *o
     else if (k == "transposetime_ns") *out = ctx->transposetime_ns;
     else if (k == "xchgtime_ns") *out = ctx->xchgtime_ns;
     else if (k == "nonempty_rows") *out = ctx->nonempty_rows;
+    else if (k == "exec_x_up_ns") *out = ctx->tl_ns[0];       // timeline of the last b200spmv_exec, from its first copy
+    else if (k == "exec_y_up_ns") *out = ctx->tl_ns[1];
+    else if (k == "exec_kernels_ns") *out = ctx->tl_ns[2];
+    else if (k == "exec_done_ns") *out = ctx->tl_ns[3];
     else if (k == "exchange_mode") *out = (uint64_t)ctx->exchange_mode;
     else if (k.rfind("slab_ns_", 0) == 0 || k.rfind("slab_nnz_", 0) == 0 || k.rfind("slab_rows_", 0) == 0 || k.rfind("slab_maxrow_", 0) == 0) {
         const int i = atoi(k.c_str() + k.rfind('_') + 1);

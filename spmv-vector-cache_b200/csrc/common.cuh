@@ -12,7 +12,7 @@
 #include "../../include/b200spmv.h"
 
 struct ncclComm;
-constexpr int Y_CHUNKS = 8;  // b200spmv_exec: row chunks of the y upload / accumulate / download pipeline
+constexpr int Y_CHUNKS = 16;  // b200spmv_exec: row chunks of the y upload / accumulate / download pipeline
 
 // ---------------------------------------------------------------------------------------
 // Device-resident matrix, one per context.
@@ -117,7 +117,18 @@ struct b200spmv_ctx {
     // [row_begin,row_end) is written by this rank)
     void *d_x = nullptr, *d_y = nullptr;
     void *d_yin = nullptr;        // the caller's y while t = A*x is computed (b200spmv_exec, accumulate)
-    cudaEvent_t ev_ychunk[8] = {nullptr};  // chunk k of the caller's y has landed in d_yin
+    // b200spmv_exec, result download: the kernel of the LAST slab is launched in Y_CHUNKS pieces of consecutive
+    // tiles; the rows below h_chunk_row[k + 1] are final once piece k and its fix-up are done (ev_rowchunk[k]),
+    // so their download (other PCIe direction) runs under the remaining pieces instead of after the whole step
+    uint32_t h_chunk_tile[Y_CHUNKS + 1] = {0}, h_chunk_row[Y_CHUNKS + 1] = {0};
+    bool chunks_ready = false;         // boundaries valid (flagged layout, last slab)
+    bool want_row_chunks = false;      // set by b200spmv_exec around the launch
+    bool did_row_chunks = false;       // ... and answered by b2_spmv_launch
+    cudaEvent_t ev_rowchunk[Y_CHUNKS] = {nullptr};
+    cudaEvent_t ev_tl[5] = {nullptr};  // exec timeline: start, x up, caller's y up, kernels done, download done
+    uint64_t tl_ns[4] = {0};           // the last four, relative to the first (stats exec_*_ns)
+    cudaStream_t d2h_stream = nullptr;
+    cudaEvent_t ev_ychunk[Y_CHUNKS] = {nullptr};  // chunk k of the caller's y has landed in d_yin
     cudaEvent_t ev_slab[64] = {nullptr};  // slice s of x has landed (b200spmv_exec uploads x slab by slab)
     bool wait_slab_events = false;
     cudaEvent_t ev_x0 = nullptr, ev_x1 = nullptr;  // around the x exchange of the last power-iteration step
@@ -213,6 +224,7 @@ int b2_build_flags(b200spmv_ctx *ctx);
 constexpr uint32_t B2_FLAG_TILE = 2048;  // entries per CTA of the flagged kernel; slabs are padded to it
 int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s);
 int b2_spmv_prepare(b200spmv_ctx *ctx, int flags, cudaStream_t s);
+bool b2_last_slab_chunkable(const b200spmv_ctx *ctx, int flags);
 void b2_profile_collect(b200spmv_ctx *ctx);
 // synth.cu
 int b2_synth_build_csc(b200spmv_ctx *ctx, int kind, uint32_t npr, uint64_t seed);

@@ -923,6 +923,26 @@ __global__ void spmv_fixup_kernel(const uint32_t *__restrict__ carry_row, const 
     y[row] = Semi<DT>::add(c, y[row]);
 }
 
+// The same for a launch cut into pieces of tiles (b200spmv_exec's download pipeline).  A row left open by tile t
+// is stored by the tile that holds the next row start, so its carries may only be added once THAT tile has run:
+// the run of carries that ends at tile e (carry_row[e + 1] differs) is added by the piece that contains tile e + 1.
+// Thread e of [lo, hi) owns the runs that end at e; same order of additions as spmv_fixup_kernel.
+template <int DT>
+__global__ void spmv_fixup_range_kernel(const uint32_t *__restrict__ carry_row, const uint64_t *__restrict__ carry_val,
+                                        uint32_t lo, uint32_t hi, uint32_t ntiles, uint64_t *__restrict__ y)
+{
+    const uint32_t e = lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= hi) return;
+    const uint32_t row = carry_row[e];
+    if (row == NO_ROW) return;
+    if (e + 1 < ntiles && carry_row[e + 1] == row) return;  // not the end of its run
+    uint32_t h = e;
+    while (h > 0 && carry_row[h - 1] == row) h--;
+    uint64_t c = carry_val[h];
+    for (uint32_t q = h + 1; q <= e; q++) c = Semi<DT>::add(c, carry_val[q]);
+    y[row] = Semi<DT>::add(c, y[row]);
+}
+
 // ---- strict order: one thread per row, reference summation order -------------------------
 template <int DT, bool READ_Y>
 __global__ void __launch_bounds__(256)
@@ -992,6 +1012,25 @@ __global__ void max_rowlen_kernel(const uint32_t *__restrict__ rowptr, uint32_t 
     if ((threadIdx.x & 31) == 0 && v > 0) atomicMax(out, v);
 }
 
+// Row below which everything is final once the tiles before tile T are done: the row that holds the entry just
+// before T's first one may go on into T, every row before it cannot (tile_seg[T] = row starts before that entry).
+__global__ void chunk_rows_kernel(const uint32_t *__restrict__ tile_seg, const uint32_t *__restrict__ seg_row, uint32_t ntiles,
+                                  uint32_t rows, int chunks, uint32_t *__restrict__ out_tile, uint32_t *__restrict__ out_row)
+{
+    const int k = threadIdx.x;
+    if (k > chunks) return;
+    const uint32_t T = (uint32_t)((uint64_t)ntiles * k / chunks);
+    uint32_t r = 0;
+    if (k == chunks) r = rows;
+    else if (T > 0) {
+        const uint32_t c = tile_seg[T];
+        r = c ? seg_row[c - 1] : 0;
+        if (r > rows) r = rows;  // NO_ROW: only pads are left
+    }
+    out_tile[k] = T;
+    out_row[k] = r;
+}
+
 int b2_build_flags(b200spmv_ctx *ctx)
 {
     DeviceCsr &m = ctx->csr;
@@ -1041,11 +1080,45 @@ int b2_build_flags(b200spmv_ctx *ctx)
         if (e == cudaSuccess) e = cudaStreamSynchronize(s);
         if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; rc = B200SPMV_ECUDA; }
     }
+    ctx->chunks_ready = false;
+    if (rc == 0) {  // download pipeline of b200spmv_exec: tile pieces of the last slab and the rows each one completes
+        const int sl = ctx->slabs - 1;
+        const uint32_t nt = ctx->h_ftile_base[sl + 1] - ctx->h_ftile_base[sl];
+        uint32_t h[2 * (Y_CHUNKS + 1)];
+        chunk_rows_kernel<<<1, 32, 0, s>>>(m.tile_seg + ctx->h_ftile_base[sl] + sl, m.seg_row + sl * stride, nt, rows, Y_CHUNKS,
+                                           segidx, segidx + Y_CHUNKS + 1);
+        cudaError_t e = cudaMemcpyAsync(h, segidx, sizeof h, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; rc = B200SPMV_ECUDA; }
+        else {
+            bool ok = true;
+            for (int k = 0; k <= Y_CHUNKS; k++) {
+                ctx->h_chunk_tile[k] = h[k];
+                ctx->h_chunk_row[k] = h[Y_CHUNKS + 1 + k];
+                if (k && (ctx->h_chunk_row[k] < ctx->h_chunk_row[k - 1] || ctx->h_chunk_tile[k] < ctx->h_chunk_tile[k - 1])) ok = false;
+            }
+            ctx->chunks_ready = ok && ctx->h_chunk_row[0] == 0 && ctx->h_chunk_row[Y_CHUNKS] == rows && ctx->h_chunk_tile[Y_CHUNKS] == nt;
+        }
+    }
     cudaFree(segidx);
     if (rc) return rc;
     ctx->flagged = true;
     ctx->colmask = 0x7FFFFFFFu;
     return 0;
+}
+
+// Will b2_spmv_launch cut the last slab's kernel into row chunks (and record ev_rowchunk[])?  Kernel 3 on the
+// flagged layout only: its tiles are consecutive pieces of the entry stream, hence of the rows.
+static bool dcsr_slab(const b200spmv_ctx *ctx, int sl)
+{
+    const uint32_t nseg = ctx->h_nseg[sl];
+    return ctx->opt_dcsr_x16 > 0 && nseg > 0 && (uint64_t)ctx->h_slab_nnz[sl] * 16 < (uint64_t)nseg * ctx->opt_dcsr_x16 &&
+           ctx->h_maxrow[sl] <= (uint32_t)ctx->opt_dcsr_maxrow;
+}
+bool b2_last_slab_chunkable(const b200spmv_ctx *ctx, int flags)
+{
+    return ctx->chunks_ready && ctx->flagged && ctx->opt_kernel == 3 && !(flags & B200SPMV_STRICT_ORDER) &&
+           ctx->order_n == 0 && ctx->local_rows > 0 && !dcsr_slab(ctx, ctx->slabs - 1);
 }
 
 static int set_persist_window(b200spmv_ctx *ctx, cudaStream_t s, const void *base, size_t bytes, bool on)
@@ -1134,8 +1207,7 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
             // hypersparse slab (fewer than opt_dcsr_x16/16 entries per non-empty row and no long row: on a skewed
             // matrix one thread with a few thousand entries holds the whole launch up): thread per non-empty row
             const uint32_t nseg = ctx->h_nseg[sl];
-            if (ctx->opt_dcsr_x16 > 0 && nseg > 0 && (uint64_t)ctx->h_slab_nnz[sl] * 16 < (uint64_t)nseg * ctx->opt_dcsr_x16 &&
-                ctx->h_maxrow[sl] <= (uint32_t)ctx->opt_dcsr_maxrow) {
+            if (dcsr_slab(ctx, sl)) {
                 const unsigned grid = b2_div_up(nseg, 256);
                 if (persist) {
                     if (read_y) spmv_dcsr_kernel<DT, true, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
@@ -1152,9 +1224,9 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
 #define B2_LAUNCH_FLAG(P, R, E)                                                                                     \
     do {                                                                                                           \
         if (ctx->opt_ept == 16)                                                                                    \
-            spmv_flag_kernel<DT, P, R, E, 16><<<nt, B2_FLAG_TILE / 16, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval, (uint32_t)ctx->opt_prefetch_tiles); \
+            spmv_flag_kernel<DT, P, R, E, 16><<<pn, B2_FLAG_TILE / 16, 0, s>>>(pci, pva, x, y, segrow, rows, ptseg, pcrow, pcval, (uint32_t)ctx->opt_prefetch_tiles); \
         else                                                                                                       \
-            spmv_flag_kernel<DT, P, R, E, 8><<<nt, B2_FLAG_TILE / 8, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval, (uint32_t)ctx->opt_prefetch_tiles);  \
+            spmv_flag_kernel<DT, P, R, E, 8><<<pn, B2_FLAG_TILE / 8, 0, s>>>(pci, pva, x, y, segrow, rows, ptseg, pcrow, pcval, (uint32_t)ctx->opt_prefetch_tiles);  \
     } while (0)
 #define B2_LAUNCH_RING(P, R, E)                                                                                     \
     do {                                                                                                           \
@@ -1199,20 +1271,54 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
                     if (read_y) { if (has_empty) B2_LAUNCH_RING(false, true, true); else B2_LAUNCH_RING(false, true, false); }
                     else { if (has_empty) B2_LAUNCH_RING(false, false, true); else B2_LAUNCH_RING(false, false, false); }
                 }
-            } else if (persist) {
-                if (read_y) { if (has_empty) B2_LAUNCH_FLAG(true, true, true); else B2_LAUNCH_FLAG(true, true, false); }
-                else { if (has_empty) B2_LAUNCH_FLAG(true, false, true); else B2_LAUNCH_FLAG(true, false, false); }
             } else {
-                if (read_y) { if (has_empty) B2_LAUNCH_FLAG(false, true, true); else B2_LAUNCH_FLAG(false, true, false); }
-                else { if (has_empty) B2_LAUNCH_FLAG(false, false, true); else B2_LAUNCH_FLAG(false, false, false); }
+                // kernel 3.  For b200spmv_exec the last slab goes out in Y_CHUNKS pieces of consecutive tiles, each
+                // followed by its own fix-up and an event: the rows a piece completes can leave for the host while
+                // the pieces after it still run (common.cuh, h_chunk_row).
+                const bool chunked = ctx->want_row_chunks && pos == ctx->slabs - 1 && b2_last_slab_chunkable(ctx, flags);
+                const int pieces = chunked ? Y_CHUNKS : 1;
+                for (int k = 0; k < pieces; k++) {
+                    const uint32_t t0 = chunked ? ctx->h_chunk_tile[k] : 0, t1 = chunked ? ctx->h_chunk_tile[k + 1] : nt;
+                    const uint32_t pn = t1 - t0;
+                    if (pn > 0) {
+                        const uint32_t *pci = ci + (size_t)t0 * B2_FLAG_TILE, *ptseg = tseg + t0;
+                        const uint64_t *pva = va + (size_t)t0 * B2_FLAG_TILE;
+                        uint32_t *pcrow = crow + t0;
+                        uint64_t *pcval = cval + t0;
+                        if (persist) {
+                            if (read_y) { if (has_empty) B2_LAUNCH_FLAG(true, true, true); else B2_LAUNCH_FLAG(true, true, false); }
+                            else { if (has_empty) B2_LAUNCH_FLAG(true, false, true); else B2_LAUNCH_FLAG(true, false, false); }
+                        } else {
+                            if (read_y) { if (has_empty) B2_LAUNCH_FLAG(false, true, true); else B2_LAUNCH_FLAG(false, true, false); }
+                            else { if (has_empty) B2_LAUNCH_FLAG(false, false, true); else B2_LAUNCH_FLAG(false, false, false); }
+                        }
+                        ctx->launches += 1;
+                    }
+                    if (k == pieces - 1 && prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
+                    if (!chunked) {
+                        spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
+                        ctx->launches += 1;
+                    } else {
+                        // carries whose run ends before the last tile this piece has run (the last piece: all that is left)
+                        const uint32_t lo = k == 0 ? 0 : std::max(t0, 1u) - 1, hi = k == pieces - 1 ? nt : std::max(t1, 1u) - 1;
+                        if (hi > lo) {
+                            spmv_fixup_range_kernel<DT><<<b2_div_up(hi - lo, 256), 256, 0, s>>>(crow, cval, lo, hi, nt, y);
+                            ctx->launches += 1;
+                        }
+                        B2_CHECK(ctx, cudaEventRecord(ctx->ev_rowchunk[k], s));
+                    }
+                }
+                ctx->did_row_chunks = ctx->did_row_chunks || chunked;
             }
 #undef B2_LAUNCH_FLAG
 #undef B2_LAUNCH_RING
 #undef B2_LAUNCH_WARP
-            if (prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
-            if (ctx->opt_kernel == 5) spmv_fixup_kernel<DT><<<b2_div_up(nw, 256), 256, 0, s>>>(wcrow, wcval, nw, y);
-            else spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
-            ctx->launches += 2;
+            if (ctx->opt_kernel == 5 || ctx->opt_kernel == 4) {
+                if (prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
+                if (ctx->opt_kernel == 5) spmv_fixup_kernel<DT><<<b2_div_up(nw, 256), 256, 0, s>>>(wcrow, wcval, nw, y);
+                else spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
+                ctx->launches += 2;
+            }
         } else if (strict) {
             const unsigned grid = b2_div_up(rows, 256);
             if (read_y) spmv_rowseq_kernel<DT, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows, ctx->colmask);

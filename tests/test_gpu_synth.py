@@ -160,3 +160,74 @@ def test_exec_accumulates_onto_a_nonzero_host_y(b2, dtype):
         assert (y == y_in + t).all()
         assert np.allclose(y, y_strict, rtol=0, atol=2 * 17 * EPS * (np.abs(y_in).max() + 16.0))
     e.close()
+
+
+@pytest.mark.parametrize("kind,rows,npr,slabs", [(1, 1 << 14, 32, 4), (1, 1 << 12, 8, 2), (2, 4099, 5, 3), (0, 5000, 3, 5)])
+def test_slab_statistics_match_host_counts(b2, kind, rows, npr, slabs):
+    """What the slab heuristics are fed with (non-empty rows of the block, longest row piece and non-empty rows of
+    every slab) is counted on the device at setup: compare with numpy on the CSR the kernels use.  A slab with a
+    long row piece must not go to the thread-per-row kernel whatever its average (dcsr_maxrow): same result."""
+    e = b2.Engine(0)
+    e.set_option("slabs", slabs)
+    e.setup_synthetic(kind, rows, rows, npr, SEED, b2.U64)
+    rp, ci, _ = e.get_csr()
+    assert e.stat("nonempty_rows") == int((np.diff(rp.astype(np.int64)) > 0).sum())
+    S = e.stat("slabs")
+    assert S == slabs
+    width = -(-rows // S)
+    width = (width + 31) // 32 * 32
+    rows_of = np.repeat(np.arange(rows), np.diff(rp.astype(np.int64)))
+    for sl in range(S):
+        inside = (ci >= sl * width) & (ci < (sl + 1) * width)
+        per_row = np.bincount(rows_of[inside], minlength=rows)
+        assert e.stat("slab_nnz_%d" % sl) == int(inside.sum())
+        assert e.stat("slab_rows_%d" % sl) == int((per_row > 0).sum())
+        assert e.stat("slab_maxrow_%d" % sl) == int(per_row.max())
+    e.fill_x_synthetic(SEED + 1)
+    e.exec_device(1, 0)
+    want = e.get_y()
+    for maxrow in (1, 1 << 30):  # never / whenever the average allows: the two kernels agree bit for bit on u64
+        f = b2.Engine(0)
+        f.set_option("slabs", slabs)
+        f.set_option("dcsr_maxrow", maxrow)
+        f.set_option("dcsr_x16", 1 << 20)
+        f.setup_synthetic(kind, rows, rows, npr, SEED, b2.U64)
+        f.fill_x_synthetic(SEED + 1)
+        f.exec_device(1, 0)
+        assert f.get_y().tobytes() == want.tobytes()
+        f.close()
+    e.close()
+
+
+@pytest.mark.parametrize("kind,rows,npr,slabs", [(0, 1 << 18, 16, 1), (0, 1 << 18, 16, 3), (1, 1 << 18, 16, 2), (2, (1 << 18) + 4099, 5, 2),
+                                                 (0, 1 << 17, 1, 1)])
+@pytest.mark.parametrize("dtype", ["u64", "f64"])
+def test_exec_download_pipeline(b2, kind, rows, npr, slabs, dtype):
+    """b200spmv_exec on vectors >= 1 MB launches the last slab's kernel in pieces of tiles and downloads the rows
+    each piece completes while the later pieces run (R-MAT: hub rows span several pieces; one entry per row: a
+    piece boundary on every kind of row boundary).  u64: bit-equal to the strict kernel, with and without
+    ACCUMULATE, several times in a row; f64: equal to the device-resident result of the same kernels."""
+    e = b2.Engine(0)
+    e.set_option("slabs", slabs)
+    e.set_option("dcsr_x16", 0)  # kernel 3 on every slab, whatever its density
+    e.setup_synthetic(kind, rows, rows, npr, SEED, DT(b2, dtype))
+    e.fill_x_synthetic(SEED + 1)
+    x = e.get_x()
+    npdt = np.uint64 if dtype == "u64" else np.float64
+    want = np.zeros(rows, dtype=npdt)
+    e.exec(x, want, b2.STRICT_ORDER)
+    e.exec_device(1, 0)
+    dev = e.get_y()
+    for rep in range(3):
+        y = np.full(rows, 7, dtype=npdt)  # overwritten, not accumulated
+        e.exec(x, y, 0)
+        assert y.tobytes() == (want if dtype == "u64" else dev).tobytes()
+    y_in = H.make_x(rows, dtype, "rand", 91)
+    y = y_in.copy()
+    e.exec(x, y, b2.ACCUMULATE)
+    if dtype == "u64":
+        assert y.tobytes() == (y_in + want).tobytes()
+    else:
+        assert (y == y_in + dev).all()
+        assert np.allclose(dev, want, rtol=0, atol=1e-9)
+    e.close()
