@@ -378,7 +378,7 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
             asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(colind + tp * B2_FLAG_TILE), "r"(B2_FLAG_TILE * 4u) : "memory");
         }
     }
-    __shared__ uint32_t s_wcnt[WARPS];
+    __shared__ __align__(16) uint32_t s_wcnt[WARPS];
     __shared__ uint32_t s_wflag[WARPS];
     __shared__ uint64_t s_wsum[WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -414,11 +414,16 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
     if (lane == 31) s_wcnt[warp] = warp_flags;
     __syncthreads();  // flag counts only: cheap, and everything below overlaps the gathers in flight
     uint32_t segs_before = __ldg(tile_seg + t) + lane_prefix, tile_flags = 0;
+    static_assert(WARPS % 4 == 0, "warp counts are read four at a time");
 #pragma unroll
-    for (int w = 0; w < WARPS; w++) {
-        const uint32_t n = s_wcnt[w];
-        if (w < warp) segs_before += n;
-        tile_flags += n;
+    for (int q = 0; q < WARPS / 4; q++) {  // one 128-bit shared load per four warps instead of a load per warp
+        const uint4 c4 = reinterpret_cast<const uint4 *>(s_wcnt)[q];
+        const uint32_t c[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (q * 4 + j < warp) segs_before += c[j];
+            tile_flags += c[j];
+        }
     }
     // the row my first flag closes, and its current y (accumulate mode): fetched now, needed last
     uint32_t close_row = NO_ROW;
@@ -456,8 +461,12 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
     const uint32_t below = bal & ((2u << lane) - 1u);
     const int start = below ? 31 - __clz(below) : 0;
     uint64_t S = acc;
+    // steps whose distance exceeds the longest open run of the warp change nothing: skip them (one REDUX
+    // instead of up to 8 shuffles when the rows are short, which column slabs make them)
+    const int span = __reduce_max_sync(0xffffffffu, lane - start);
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
+        if (d > span) break;
         const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
         if (lane - d >= start) S = Semi<DT>::add(n, S);
     }
