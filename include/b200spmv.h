@@ -74,7 +74,7 @@ B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx ma
  * still on the wire), "exchange" (with own_slabs: 2 = the other blocks are pulled from the peers' x over
  * NVLink by the copy engines through CUDA IPC mappings, block by block, each block's slabs starting when
  * it has landed -- the default, falls back to 1 where peers cannot be mapped; 1 = one NCCL all-gather under
- * the own-block slabs), "pull_streams" (copy streams of exchange 2, default 2).  Stat "exchange_mode"
+ * the own-block slabs), "pull_streams" (copy streams of exchange 2, default 1).  Stat "exchange_mode"
  * reports what the last b200spmv_power_iterate did (0 = NCCL all-gather after the step). */
 B200SPMV_API int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t value);
 

@@ -60,7 +60,7 @@ struct b200spmv_ctx {
     int opt_prefetch_tiles = 148; // kernel 3: L2 bulk prefetch (UBLKPF) of the tile this many CTAs ahead (0 = off)
     int opt_own_slabs = 0;        // 1: align the slabs with the ranks' blocks of x (set before setup; see own_lo)
     int opt_exchange = 2;         // with own_slabs: 1 = NCCL all-gather under the own-block slabs, 2 = peer pulls
-    int opt_pull_streams = 2;     // copy streams the peer pulls are spread over
+    int opt_pull_streams = 1;     // copy streams the peer pulls are spread over
     int opt_dcsr_maxrow = 64;     // ... and only when no row piece of the slab is longer than this
     int opt_prefetch_x = 0;       // 1: stream each slab's slice of x into L2 (UBLKPF) before its kernel
     int opt_graph = 1;            // b200spmv_exec_device replays a captured CUDA graph of one step
