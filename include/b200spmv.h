@@ -69,6 +69,11 @@ B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx ma
  * DESIGN.md 3.2; default 3), "ept", "ctas_per_sm" (kernel tuning), "world" then "rank" (take the
  * place of rank r of w in the nnz-balanced row-block split WITHOUT a communicator: a single SpMV
  * needs no collective; b200spmv_power_iterate does and refuses).
+ * Kernel selection per slab: "dcsr_x16" (thread-per-row kernel when a slab holds fewer than value/16 entries
+ * per non-empty row, default 96; 0 = never) and "dcsr_maxrow" (... and no row piece longer than this, default
+ * 64); "prefetch_tiles" (kernel 3: L2 bulk prefetch distance in CTAs, default 148), "prefetch_x" (1 = stream a
+ * slab's slice of x into L2 before its kernel; measured useless, default 0), "graph" (b200spmv_exec_device
+ * replays a CUDA graph of one step, default 1).
  * For iterated SpMV over several ranks: "own_slabs" (1 = cut the column slabs along the ranks' blocks of
  * x, so that b200spmv_power_iterate can run the slabs of a rank's own block while the other blocks are
  * still on the wire), "exchange" (with own_slabs: 2 = the other blocks are pulled from the peers' x over
@@ -121,8 +126,11 @@ B200SPMV_API int b200spmv_get_csc(b200spmv_ctx *ctx, uint32_t *colptr, uint32_t 
 /* ---- statistics: SpMV::statInt / statKeys (software/SpMV.h:28-29) ---------------------- */
 /* keys: rows cols nz local_rows local_nz row_begin row_end spmvtime_ns xfertime_ns
  * setuptime_ns transposetime_ns xchgtime_ns (x exchange of the last power-iteration step) slabs l2_persist_bytes l2_bytes sms gpus rank mode
- * launches cuda_error tiles; with option "profile"=1 also merge_kernel_ns and
- * merge_kernel_launches (CUDA-event time of the merge-path kernel alone, for the roofline) */
+ * launches cuda_error tiles nonempty_rows (of this rank's block) exchange_mode; per slab i: slab_nnz_<i>,
+ * slab_rows_<i> (non-empty rows), slab_maxrow_<i> (longest row piece); timeline of the last b200spmv_exec from
+ * its first copy: exec_x_up_ns exec_y_up_ns exec_kernels_ns exec_done_ns; with option "profile"=1 also
+ * merge_kernel_ns and merge_kernel_launches (CUDA-event time of the SpMV kernel alone, for the roofline) and
+ * slab_ns_<i> (the same per slab) */
 B200SPMV_API int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *out);
 
 /* ---- multi-GPU: one context (process) per GPU ------------------------------------------ */
