@@ -74,6 +74,9 @@ B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx ma
  * 64); "prefetch_tiles" (kernel 3: L2 bulk prefetch distance in CTAs, default 148), "prefetch_x" (1 = stream a
  * slab's slice of x into L2 before its kernel; measured useless, default 0), "graph" (b200spmv_exec_device
  * replays a CUDA graph of one step, default 1).
+ * "pin_host" (1 = b200spmv_exec page-locks the caller's pageable x / y in place with cudaHostRegister the first
+ * time it sees them, vectors >= 256 KB, and keeps them so until another pointer is passed or the context is
+ * destroyed -- for callers whose vectors outlive the context's use of them, as SpMV objects' do; default 0).
  * For iterated SpMV over several ranks: "own_slabs" (1 = cut the column slabs along the ranks' blocks of
  * x, so that b200spmv_power_iterate can run the slabs of a rank's own block while the other blocks are
  * still on the wire), "exchange" (with own_slabs: 2 = the other blocks are pulled from the peers' x over

@@ -69,8 +69,7 @@ extern "C" void b200spmv_destroy(b200spmv_ctx *ctx)
     cudaSetDevice(ctx->device);
     b2_comm_destroy(ctx);
     release_matrix(ctx);
-    if (ctx->pin_x) cudaFreeHost(ctx->pin_x);
-    if (ctx->pin_y) cudaFreeHost(ctx->pin_y);
+    for (int i = 0; i < 2; i++) if (ctx->reg_ptr[i]) { cudaHostUnregister(ctx->reg_ptr[i]); cudaGetLastError(); }
     if (ctx->d_norm) cudaFree(ctx->d_norm);
     free(ctx->h_row_splits);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
@@ -105,6 +104,7 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "prefetch_tiles") ctx->opt_prefetch_tiles = (int)std::max<int64_t>(0, value);
     else if (k == "graph") ctx->opt_graph = (int)value;
     else if (k == "prefetch_x") ctx->opt_prefetch_x = (int)value;
+    else if (k == "pin_host") ctx->opt_pin_host = value != 0;
     else if (k == "dcsr_maxrow") ctx->opt_dcsr_maxrow = (int)value;
     else if (k == "exchange") { if (value < 1 || value > 2) return b2_fail(ctx, B200SPMV_EINVAL, "exchange must be 1 or 2"); ctx->opt_exchange = (int)value; }
     else if (k == "pull_streams") { if (value < 1 || value > 4) return b2_fail(ctx, B200SPMV_EINVAL, "pull_streams must be 1..4"); ctx->opt_pull_streams = (int)value; }
@@ -291,6 +291,22 @@ extern "C" int b200spmv_setup_synthetic(b200spmv_ctx *ctx, int kind, uint32_t ro
 
 // ---- exec -----------------------------------------------------------------------------------
 
+// option pin_host: page-lock a pageable host vector where it lies (once per pointer); failure is not an error,
+// the copies then go through the driver's staging buffers as before
+static void pin_in_place(b200spmv_ctx *ctx, int slot, const void *ptr, size_t bytes)
+{
+    if (!ctx->opt_pin_host || bytes < (256u << 10)) return;
+    if (ctx->reg_ptr[slot] == ptr && ctx->reg_bytes[slot] >= bytes) return;
+    if (ctx->reg_ptr[slot]) { cudaHostUnregister(ctx->reg_ptr[slot]); cudaGetLastError(); ctx->reg_ptr[slot] = nullptr; }
+    cudaPointerAttributes pa;
+    if (cudaPointerGetAttributes(&pa, ptr) == cudaSuccess && pa.type != cudaMemoryTypeUnregistered) return;  // pinned already
+    cudaGetLastError();
+    if (cudaHostRegister(const_cast<void *>(ptr), bytes, cudaHostRegisterDefault) == cudaSuccess) {
+        ctx->reg_ptr[slot] = const_cast<void *>(ptr);
+        ctx->reg_bytes[slot] = bytes;
+    } else cudaGetLastError();
+}
+
 // y[i] = yin[i] (+) y[i]
 template <int DT>
 __global__ void vec_accumulate_kernel(uint64_t *__restrict__ y, const uint64_t *__restrict__ yin, uint64_t n)
@@ -311,6 +327,8 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
     const uint64_t t0 = now_ns();
     uint64_t *yh = (uint64_t *)y_host + ctx->row_begin;
     uint64_t *yd = (uint64_t *)ctx->d_y + ctx->row_begin;
+    pin_in_place(ctx, 0, x_host, (size_t)ctx->cols * 8);
+    pin_in_place(ctx, 1, yh, (size_t)ctx->local_rows * 8);
     // x goes up slab slice by slab slice on the copy stream: the kernels of slab s only gather from slice s,
     // so they start as soon as it has landed (b2_spmv_launch waits on ev_slab[s]) while the rest still uploads
     const bool sliced_x = ctx->slabs > 1 && !(flags & B200SPMV_STRICT_ORDER) && (size_t)ctx->cols * 8 >= (8u << 20);

@@ -62,6 +62,7 @@ struct b200spmv_ctx {
     int opt_exchange = 2;         // with own_slabs: 1 = NCCL all-gather under the own-block slabs, 2 = peer pulls
     int opt_pull_streams = 1;     // copy streams the peer pulls are spread over
     int opt_dcsr_maxrow = 64;     // ... and only when no row piece of the slab is longer than this
+    int opt_pin_host = 0;         // see reg_ptr
     int opt_prefetch_x = 0;       // 1: stream each slab's slice of x into L2 (UBLKPF) before its kernel
     int opt_graph = 1;            // b200spmv_exec_device replays a captured CUDA graph of one step
     int opt_ablate = 0;           // kernel 5 only, measurement: see spmv_flag_warp_kernel
@@ -133,8 +134,11 @@ struct b200spmv_ctx {
     bool wait_slab_events = false;
     cudaEvent_t ev_x0 = nullptr, ev_x1 = nullptr;  // around the x exchange of the last power-iteration step
     uint64_t xchgtime_ns = 0;
-    void *pin_x = nullptr, *pin_y = nullptr;  // pinned staging for pageable host vectors
-    size_t pin_x_bytes = 0, pin_y_bytes = 0;
+    // option pin_host: the caller's pageable x / y are page-locked in place (cudaHostRegister) the first time they
+    // are seen and stay so until another pointer takes the slot or the context goes: SpMV objects keep their
+    // vectors for life (software/SpMV.h:31-33), so every exec after the first copies at pinned speed
+    void *reg_ptr[2] = {nullptr, nullptr};
+    size_t reg_bytes[2] = {0, 0};
     bool persist_set = false;
 
     // multi-GPU

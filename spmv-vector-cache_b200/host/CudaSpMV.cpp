@@ -37,6 +37,8 @@ CudaSpMV::CudaSpMV(SparseMatrix *A, SpMVData *x, SpMVData *y, const CudaSpMVOpti
     }
     if (opt.slabs > 0) b200spmv_set_option(m_ctx, "slabs", opt.slabs);
     if (opt.requireAligned) b200spmv_set_option(m_ctx, "require_aligned", 1);
+    // m_x / m_y live as long as this object (SpMV.h:31-33): page-lock them in place on first use
+    b200spmv_set_option(m_ctx, "pin_host", 1);
     m_lastRc = b200spmv_setup_csc(m_ctx, A->getRows(), A->getCols(), A->getNz(), A->getIndPtrs(), A->getInds(),
                                   A->getNzData(), kDtype, opt.indexMask);
     if (m_lastRc != 0) {
