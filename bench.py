@@ -251,6 +251,7 @@ def run_ours(args):
         return float(t.item())
 
     power = args.workload == "banded-power" and not args.shard
+    step_stats = {}
     sampler = ClockSampler(local)
     # ---- device-resident timing: W warm-up, then exactly K steps --------------------------
     if power:
@@ -265,6 +266,7 @@ def run_ours(args):
     else:
         ms = eng.exec_device(args.steps, flags)  # CUDA events on the launching stream, one pair per step
         ms_total = float(ms.sum())
+        step_stats = {"ms_best": float(ms.min()), "ms_median": float(np.median(ms))}  # this rank's steps
     barrier()
     launches = eng.stat("launches") - launches0
     t_dev = max_over_ranks(ms_total) * 1e-3
@@ -317,6 +319,7 @@ def run_ours(args):
                                     "row blocks + x all-gather per step",
                        "l2": "inputs (%.1f GB) larger than L2; no flush" % (b_alg(nnz, rows, cols) / 1e9),
                        "slabs": slabs, "persist_window": not args.no_persist, "setup_s": round(setup_s, 2),
+                       "setup_amortised_over_steps": int(round(setup_s / (t_dev / args.steps))), **step_stats,
                        **({"x_exchange_ms_last_step": eng.stat("xchgtime_ns") * 1e-6, "exchange": ["NCCL all-gather after the step", "NCCL all-gather under the own-block slabs",
                                         "peer pulls block by block under the slabs"][eng.stat("exchange_mode")]}
                           if power and world > 1 else {}),
