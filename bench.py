@@ -30,6 +30,9 @@ WORKLOADS = {
     "uniform": (0, 1 << 24, 32, "synthetic uniform-random 16M x 16M, 32 nnz/row, fp64"),
     "rmat": (1, 1 << 26, 32, "synthetic R-MAT scale 26 (64M rows, 2^31 nnz), fp64"),
     "banded-power": (2, 1 << 27, 5, "power iteration, 128M-row banded(11)+5 random, fp64"),
+    # locality probes: here HBM, not the gather path, should bind
+    "band": (3, 1 << 24, 16, "synthetic pure band 16M x 16M, 16 consecutive columns per row, fp64"),
+    "banded": (2, 1 << 24, 5, "synthetic banded(11)+5 random 16M x 16M, fp64"),
 }
 
 
@@ -38,8 +41,7 @@ def b_alg(nnz, rows, cols):
     return 12 * nnz + 4 * (rows + 1) + 8 * cols + 8 * rows
 
 
-KERNEL_NAMES = {0: "spmv_rowseq_kernel", 1: "spmv_merge_kernel", 2: "spmv_merge_tma_kernel", 3: "spmv_flag_kernel",
-                4: "spmv_flag_ring_kernel", 5: "spmv_flag_warp_kernel"}
+KERNEL_NAMES = {0: "spmv_rowseq_kernel", 3: "spmv_flag_kernel", 6: "spmv_stream_kernel"}
 
 
 def recorded_traffic(workload, rows, cols, slabs, mode, world, flags):
@@ -211,10 +213,9 @@ def run_ours(args):
         eng.set_option("slabs", args.slabs)
     if args.kernel:
         eng.set_option("kernel", args.kernel)
-    if args.ept:
-        eng.set_option("ept", args.ept)
-    if args.ctas:
-        eng.set_option("ctas_per_sm", args.ctas)
+    for opt in ("stream_db", "stream_pf", "stream_occ", "stream_vchunks"):
+        if getattr(args, opt) is not None:
+            eng.set_option(opt, getattr(args, opt))
     if args.prefetch is not None:
         eng.set_option("prefetch_tiles", args.prefetch)
     if args.graph is not None:
@@ -229,8 +230,6 @@ def run_ours(args):
         eng.set_option("exchange", 2 if args.exchange == "pull" else 1)
         if args.pull_streams:
             eng.set_option("pull_streams", args.pull_streams)
-    if args.ablate:
-        eng.set_option("ablate", args.ablate)
     t0 = time.perf_counter()
     eng.setup_synthetic(kind, rows, cols, npr, SEED, b2.F64)
     setup_s = time.perf_counter() - t0
@@ -250,7 +249,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    power = args.workload == "banded-power" and not args.shard
+    power = args.workload == "banded-power" and not args.shard and not args.no_power
     step_stats = {}
     sampler = ClockSampler(local)
     # ---- device-resident timing: W warm-up, then exactly K steps --------------------------
@@ -359,13 +358,14 @@ def main():
     ap.add_argument("--dcsr", type=int, default=None, help="hypersparse-slab threshold x16 (0 = never use spmv_dcsr_kernel)")
     ap.add_argument("--cols", type=int, default=0, help="override the column count (experiments only)")
     ap.add_argument("--slabs", type=int, default=0)
-    ap.add_argument("--ept", type=int, default=0, help="entries per thread of kernel 3 (8 or 16)")
-    ap.add_argument("--kernel", type=int, default=0,
-                    help="1 merge-path LDG-staged, 2 merge-path TMA-staged, 3 flagged, 4 flagged persistent TMA ring (default)")
+    ap.add_argument("--kernel", type=int, default=0, help="6 flagged segmented sum by persistent warps (default), 3 one tile per CTA")
+    ap.add_argument("--stream-db", type=int, default=None, help="kernel 6: register double buffer of the entry streams (default 1)")
+    ap.add_argument("--stream-pf", type=int, default=None, help="kernel 6: L2 bulk prefetch distance in warp steps (default 0)")
+    ap.add_argument("--stream-occ", type=int, default=None, help="kernel 6: CTAs per SM")
+    ap.add_argument("--stream-vchunks", type=int, default=None, help="kernel 6: chunks per warp")
+    ap.add_argument("--no-power", action="store_true", help="banded-power: time plain SpMV steps instead of the power iteration")
     ap.add_argument("--prefetch", type=int, default=None, help="kernel 3: L2 bulk prefetch distance in tiles")
     ap.add_argument("--graph", type=int, default=None, help="0: do not replay a CUDA graph in exec_device")
-    ap.add_argument("--ablate", type=int, default=0, help="kernel 5 ablation level (measurement only; results are wrong)")
-    ap.add_argument("--ctas", type=int, default=0, help="persistent CTAs per SM of kernel 4")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
     ap.add_argument("--no-persist", action="store_true")
     ap.add_argument("--exchange", choices=["pull", "overlap", "nccl"], default="pull",

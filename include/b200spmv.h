@@ -47,6 +47,7 @@ typedef struct b200spmv_ctx b200spmv_ctx;
 #define B200SPMV_SYNTH_UNIFORM 0
 #define B200SPMV_SYNTH_RMAT 1
 #define B200SPMV_SYNTH_BANDED 2
+#define B200SPMV_SYNTH_BAND 3 /* pure band of nnz_per_row consecutive columns (locality / HBM-roofline probe) */
 
 /* error codes */
 #define B200SPMV_OK 0

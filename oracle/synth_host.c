@@ -22,10 +22,15 @@ ORACLE_API uint64_t synth_host_nnz(int kind, uint32_t rows, uint32_t npr)
         for (uint32_t r = 0; r < rows; r++) n += synth_band_count(r, rows) + npr;
         return n;
     }
+    if (kind == SYNTH_BAND) {
+        uint64_t n = 0;
+        for (uint32_t r = 0; r < rows; r++) n += synth_row_len(kind, r, rows, npr);
+        return n;
+    }
     return (uint64_t)rows * npr;
 }
 
-/* CSR of the row-generated kinds (UNIFORM, BANDED). */
+/* CSR of the row-generated kinds (UNIFORM, BANDED, BAND). */
 ORACLE_API void synth_host_csr(int kind, uint64_t seed, uint32_t rows, uint32_t cols, uint32_t npr,
                                int dtype_u64, uint32_t *rowptr, uint32_t *colind, uint64_t *vals)
 {

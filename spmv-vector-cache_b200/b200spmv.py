@@ -9,11 +9,12 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb200spmv.so")
+# B200SPMV_LIB: a measurement build of the same library (make ablate), experiments only
+LIB_PATH = os.environ.get("B200SPMV_LIB") or os.path.join(HERE, "libb200spmv.so")
 
 F64, U64 = 0, 1
 ACCUMULATE, STRICT_ORDER, NO_PERSIST = 1, 2, 4
-SYNTH_UNIFORM, SYNTH_RMAT, SYNTH_BANDED = 0, 1, 2
+SYNTH_UNIFORM, SYNTH_RMAT, SYNTH_BANDED, SYNTH_BAND = 0, 1, 2, 3
 
 EXPORTS = [
     "b200spmv_create", "b200spmv_destroy", "b200spmv_last_error", "b200spmv_set_option",

@@ -19,7 +19,7 @@ static void release_matrix(b200spmv_ctx *ctx)
     DeviceCsr &m = ctx->csr;
     b2_free(m.rowptr); b2_free(m.colind);
     { uint64_t *v = (uint64_t *)m.vals; b2_free(v); m.vals = nullptr; }
-    b2_free(m.tile_row); b2_free(m.tile_nz); b2_free(m.carry_row);
+    b2_free(m.carry_row);
     b2_free(m.seg_row); b2_free(m.tile_seg); b2_free(m.warp_seg);
     { uint64_t *v = (uint64_t *)m.carry_val; b2_free(v); m.carry_val = nullptr; }
     b2_free(ctx->csc_colptr); b2_free(ctx->csc_rowind);
@@ -98,8 +98,11 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "persist_bytes") ctx->opt_persist_bytes = value;
     else if (k == "require_aligned") ctx->opt_require_aligned = (int)value;
     else if (k == "keep_csc") ctx->opt_keep_csc = (int)value;
-    else if (k == "ept") { if (value != 8 && value != 16) return b2_fail(ctx, B200SPMV_EINVAL, "ept must be 8 or 16"); ctx->opt_ept = (int)value; }
-    else if (k == "kernel") { if (value < 1 || value > 5) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 1..5"); ctx->opt_kernel = (int)value; }
+    else if (k == "kernel") { if (value != 3 && value != 6) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 3 or 6"); ctx->opt_kernel = (int)value; }
+    else if (k == "stream_db") ctx->opt_stream_db = value != 0;
+    else if (k == "stream_pf") { if (value < 0 || value > 64) return b2_fail(ctx, B200SPMV_EINVAL, "stream_pf must be 0..64"); ctx->opt_stream_pf = (int)value; }
+    else if (k == "stream_occ") { if (value < 0 || value > 8) return b2_fail(ctx, B200SPMV_EINVAL, "stream_occ must be 0..8"); ctx->opt_stream_occ = (int)value; }
+    else if (k == "stream_vchunks") { if (value < 1 || value > 64) return b2_fail(ctx, B200SPMV_EINVAL, "stream_vchunks must be 1..64"); ctx->opt_stream_vchunks = (int)value; }
     else if (k == "dcsr_x16") ctx->opt_dcsr_x16 = (int)value;
     else if (k == "prefetch_tiles") ctx->opt_prefetch_tiles = (int)std::max<int64_t>(0, value);
     else if (k == "graph") ctx->opt_graph = (int)value;
@@ -112,8 +115,6 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
         if (ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "set own_slabs before setup");
         ctx->opt_own_slabs = value != 0;
     }
-    else if (k == "ablate") ctx->opt_ablate = (int)value;
-    else if (k == "ctas_per_sm") { if (value < 1 || value > 8) return b2_fail(ctx, B200SPMV_EINVAL, "ctas_per_sm must be 1..8"); ctx->opt_ctas_per_sm = (int)value; }
     else if (k == "world" || k == "rank") {
         // row-block sharding without a communicator: a single SpMV needs no collective, so a
         // rank can be given its place by hand (tests: all ranks of a split, one after the other, on one GPU)
@@ -224,7 +225,6 @@ static int csc_to_csr(b200spmv_ctx *ctx, uint32_t index_mask)
         b2_free(ctx->csc_colptr); b2_free(ctx->csc_rowind);
         uint64_t *v = (uint64_t *)ctx->csc_vals; b2_free(v); ctx->csc_vals = nullptr;
     }
-    B2_TRY(b2_build_tiles(ctx));
     B2_TRY(b2_build_flags(ctx));
     { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->cols)); ctx->d_x = v; }
     { uint64_t *v = nullptr; B2_TRY(b2_alloc(ctx, &v, ctx->rows)); ctx->d_y = v; }

@@ -25,17 +25,13 @@ struct DeviceCsr {
     uint32_t *rowptr = nullptr;  // [slabs][local_rows+1], absolute offsets into colind/vals
     uint32_t *colind = nullptr;  // [local_nnz (+pad)], GLOBAL column ids
     void *vals = nullptr;        // [local_nnz (+pad)] 8-byte
-    // merge-path tiling, one table per slab: tile t starts at (row, nz) = tile_row[t], tile_nz[t]
-    uint32_t *tile_row = nullptr;
-    uint32_t *tile_nz = nullptr;
-    uint32_t *tile_base = nullptr;  // [slabs+1] first tile of each slab (host copy in h_tile_base)
-    // flagged format (kernel 3): bit 31 of colind marks the first entry of a row; seg_row maps
+    // flagged format (kernels 3 and 6): bit 31 of colind marks the first entry of a row; seg_row maps
     // the n-th non-empty row of a slab to its row id; tile_seg[t] = flags before entry t*FLAG_TILE
     uint32_t *seg_row = nullptr;    // [slabs][rowptr_stride]  (nseg+1 used, last = NO_ROW)
     uint32_t *tile_seg = nullptr;   // [slabs] tables, slab s at h_ftile_base[s] + s, ntiles_s + 1 entries
-    uint32_t *warp_seg = nullptr;   // same per 256-entry warp tile (kernel 5), slab s at 8*h_ftile_base[s] + s
-    uint32_t *carry_row = nullptr;  // [tiles] row of the tile's carry-out
-    void *carry_val = nullptr;      // [tiles] 8-byte partial of that row
+    uint32_t *warp_seg = nullptr;   // same per 256-entry warp step (kernel 6), slab s at 8*h_ftile_base[s] + s
+    uint32_t *carry_row = nullptr;  // [8 * tiles] row of a tile's (kernel 3) / chunk's (kernel 6) carry-out
+    void *carry_val = nullptr;      // ... and the 8-byte partial of that row
 };
 
 struct b200spmv_ctx {
@@ -54,8 +50,11 @@ struct b200spmv_ctx {
     int64_t opt_persist_bytes = 0;  // 0 = device max
     int opt_require_aligned = 0;
     int opt_keep_csc = 0;
-    int opt_kernel = 3;           // 1 = merge-path LDG-staged, 2 = merge-path TMA-staged, 3 = flagged segmented sum,
-                                  // 4 = flagged, persistent CTAs with a TMA-fed shared-memory ring, 5 = flagged, warp-sized tiles
+    int opt_kernel = 6;           // 3 = flagged segmented sum, one tile per CTA; 6 = the same by persistent warps (spmv.cu)
+    int opt_stream_db = 1;        // kernel 6: register double buffer for the entry streams
+    int opt_stream_pf = 0;        // kernel 6: L2 bulk prefetch (UBLKPF) distance in warp steps (0 = off)
+    int opt_stream_occ = 0;       // kernel 6: CTAs per SM (0 = what the launch bounds allow: 2 with the double buffer, else 3)
+    int opt_stream_vchunks = 1;   // kernel 6: chunks per warp (1 = one contiguous chunk per warp)
     int opt_dcsr_x16 = 96;        // slabs with < this/16 (= 6) entries per non-empty row use spmv_dcsr_kernel (0 = never)
     int opt_prefetch_tiles = 148; // kernel 3: L2 bulk prefetch (UBLKPF) of the tile this many CTAs ahead (0 = off)
     int opt_own_slabs = 0;        // 1: align the slabs with the ranks' blocks of x (set before setup; see own_lo)
@@ -65,9 +64,6 @@ struct b200spmv_ctx {
     int opt_pin_host = 0;         // see reg_ptr
     int opt_prefetch_x = 0;       // 1: stream each slab's slice of x into L2 (UBLKPF) before its kernel
     int opt_graph = 1;            // b200spmv_exec_device replays a captured CUDA graph of one step
-    int opt_ablate = 0;           // kernel 5 only, measurement: see spmv_flag_warp_kernel
-    int opt_ctas_per_sm = 4;      // persistent grid of kernel 4 = sms * this
-    int opt_ept = 8;              // entries per thread of kernel 3 (8 or 16)
     int opt_profile = 0;          // 1: bracket every merge-kernel launch with events (bench roofline)
 
     // matrix
@@ -99,7 +95,6 @@ struct b200spmv_ctx {
     bool peers_open = false, peers_failed = false;
     int exchange_mode = 0;             // what the last power iteration did: 0 after the step (NCCL), 1 all-gather
                                        // under the own-block slabs, 2 peer pulls block by block
-    uint32_t h_tile_base[65] = {0};
     uint32_t h_ftile_base[65] = {0};   // flagged-kernel tiles per slab (prefix)
     uint64_t h_slab_off[65] = {0};     // entry offset of each slab in colind/vals (padded to FLAG_TILE)
     uint32_t h_slab_nnz[64] = {0};
@@ -108,7 +103,7 @@ struct b200spmv_ctx {
     bool flagged = false;              // colind carries row-start flags in bit 31
     uint32_t colmask = 0xFFFFFFFFu;    // mask that strips the flag
     uint64_t padded_nnz = 0;
-    uint32_t total_tiles = 0;
+    uint32_t total_tiles = 0;          // 2048-entry tiles over all slabs
     DeviceCsr csr;
     // CSC copy (rank-local entries, global ids)
     uint32_t *csc_colptr = nullptr, *csc_rowind = nullptr;
@@ -223,9 +218,8 @@ int b2_add_u32(b200spmv_ctx *ctx, uint32_t *a, uint64_t n, uint32_t add, cudaStr
 int b2_count_nonempty(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *key, uint32_t key_mask,
                       uint32_t key_sub, uint64_t *out, cudaStream_t s);
 // spmv.cu
-int b2_build_tiles(b200spmv_ctx *ctx);
 int b2_build_flags(b200spmv_ctx *ctx);
-constexpr uint32_t B2_FLAG_TILE = 2048;  // entries per CTA of the flagged kernel; slabs are padded to it
+constexpr uint32_t B2_FLAG_TILE = 2048;  // entries per CTA of kernel 3 (8 warp steps of kernel 6); slabs are padded to it
 int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s);
 int b2_spmv_prepare(b200spmv_ctx *ctx, int flags, cudaStream_t s);
 bool b2_last_slab_chunkable(const b200spmv_ctx *ctx, int flags);

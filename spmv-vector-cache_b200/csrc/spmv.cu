@@ -1,17 +1,24 @@
 // spmv.cu -- the hot path: y (+)= A*x on the device-resident CSR (software/SoftwareSpMV.cpp:59-64
 // after the CSC->CSR transpose).
 //
-//   spmv_merge_kernel : nnz-balanced merge-path SpMV.  The merge of the row-end offsets with
-//       the nnz indices is cut into tiles of MP_TILE items; a CTA stages one tile's products
-//       val*x[col] in shared memory with 128-bit streaming loads of indices and values, then
-//       every thread walks MP_IPT merge items, rows that straddle threads are completed from
-//       the neighbours' carries, rows that straddle tiles through a carry-out fixed up by
-//       spmv_fixup_kernel.  Re-associates fp64 sums (tolerance mode); u64 is exact.
+//   spmv_stream_kernel (6, default) : flagged segmented sum by PERSISTENT, autonomous warps.  Every warp owns a
+//       contiguous chunk of the slab's entry stream and walks it 256 entries at a time; the two 12 B/entry
+//       streams of the NEXT step are already in flight (register double buffer, optional L2 bulk prefetch)
+//       while the x gathers and the row logic of the current one run, the open row travels in a register
+//       from step to step, and only one carry per chunk is left for spmv_fixup_kernel.  No shared memory,
+//       no block barrier, no row pointers.
+//   spmv_flag_kernel (3) : the same flagged arithmetic with one 2048-entry tile per (non-persistent) CTA.
+//       Kept because its tiles are consecutive pieces of the rows: b200spmv_exec launches the last slab in
+//       pieces of tiles and sends finished rows to the host while later pieces run.
+//   spmv_dcsr_kernel : hypersparse slabs, one thread per non-empty row (storage order: bit-exact in fp64).
 //   spmv_rowseq_kernel : one thread per row, entries in CSR (= reference) order, separate
 //       multiply and add: fp64 results memcmp-equal to SoftwareSpMV (strict mode).
 //
 // Column slabs: with S > 1 the CSR is stored slab-major and the kernels run slab by slab, so
-// the x slice gathered at any time fits the L2 set-aside (the "vector cache").
+// the x slice gathered at any time fits L2 (the "vector cache").
+// The merge-path kernels (1, 2) and the TMA-ring kernel (4) of round 1 lost to kernel 3 by 2.5-2.9x and were
+// removed; kernel 5 (warp tiles, one carry per 256 entries) is subsumed by kernel 6.  DESIGN.md 3.4 keeps
+// their numbers.
 #include <algorithm>
 #include <vector>
 
@@ -19,303 +26,13 @@
 
 namespace {
 
-constexpr int MP_THREADS = 256;
-constexpr int MP_IPT = 8;
-constexpr int MP_TILE = MP_THREADS * MP_IPT;  // merge items per tile
 constexpr uint32_t NO_ROW = 0xFFFFFFFFu;
-
-// ---- merge-path partition (once per matrix) --------------------------------------------
-// rowptr: this slab's [rows+1] absolute offsets.  Tile t of the slab starts at merge diagonal
-// t*MP_TILE; writes (rows consumed, absolute nz offset) for t in [0, ntiles].
-__global__ void tile_search_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, uint32_t ntiles,
-                                   uint32_t *__restrict__ tile_row, uint32_t *__restrict__ tile_nz)
-{
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t > ntiles) return;
-    const uint32_t nz_begin = rowptr[0];
-    const uint64_t nnz = (uint64_t)rowptr[rows] - nz_begin;
-    const uint64_t items = (uint64_t)rows + nnz;
-    const uint64_t diag = min((unsigned long long)t * MP_TILE, (unsigned long long)items);
-    uint64_t lo = diag > nnz ? diag - nnz : 0;
-    uint64_t hi = min((unsigned long long)diag, (unsigned long long)rows);
-    while (lo < hi) {
-        const uint64_t mid = (lo + hi) >> 1;
-        // row-end item `mid` precedes nnz item (diag-mid-1) iff rowend[mid] <= that nnz index
-        if ((uint64_t)(rowptr[mid + 1] - nz_begin) <= diag - mid - 1) lo = mid + 1; else hi = mid;
-    }
-    tile_row[t] = (uint32_t)lo;
-    tile_nz[t] = nz_begin + (uint32_t)(diag - lo);
-}
 
 template <bool PERSIST>
 __device__ __forceinline__ uint64_t load_x(const uint64_t *__restrict__ x, uint32_t col, uint64_t pol)
 {
     if (PERSIST) return ld_gather_u64(x + col, pol);
     return __ldg(reinterpret_cast<const unsigned long long *>(x + col));
-}
-
-struct MergeSmem {
-    uint64_t prod[MP_TILE + 4];
-    uint64_t yrow[MP_TILE];
-    uint64_t cval[MP_THREADS];
-    uint32_t rowend[MP_TILE + 1];
-    uint32_t crow[MP_THREADS];
-};
-
-// ---- merge-path SpMV, one tile per CTA ---------------------------------------------------
-// READ_Y: the rows completed here start from the y already in memory (accumulate mode, or any
-// slab after the first); otherwise from the additive identity.
-template <int DT, bool PERSIST, bool READ_Y>
-__global__ void __launch_bounds__(MP_THREADS)
-spmv_merge_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ colind,
-                  const uint64_t *__restrict__ vals, const uint64_t *__restrict__ x,
-                  uint64_t *__restrict__ y, uint32_t rows, const uint32_t *__restrict__ tile_row,
-                  const uint32_t *__restrict__ tile_nz, uint32_t *__restrict__ carry_row,
-                  uint64_t *__restrict__ carry_val, uint32_t colmask)
-{
-    __shared__ __align__(16) MergeSmem sm;
-    const uint32_t t = blockIdx.x;
-    const int tid = threadIdx.x;
-    const uint32_t r0 = tile_row[t], r1 = tile_row[t + 1];
-    const uint32_t nz0 = tile_nz[t], nz1 = tile_nz[t + 1];
-    const uint32_t tile_rows = r1 - r0, tile_nnz = nz1 - nz0;
-    const uint32_t tile_items = tile_rows + tile_nnz;
-
-    // (1) row-end offsets of rows r0..r1 (r1 = the row left open at the end of the tile)
-    for (uint32_t i = tid; i <= tile_rows; i += MP_THREADS) {
-        const uint32_t r = r0 + i;
-        sm.rowend[i] = (r < rows) ? rowptr[r + 1] : 0xFFFFFFFFu;
-    }
-    // (2) stage products: groups of 4 entries from a 16-byte aligned base
-    const uint32_t base = nz0 & ~3u;
-    const uint32_t ngroups = (nz1 - base + 3) >> 2;
-    const uint64_t pol_stream = policy_evict_first(), pol_keep = policy_evict_last();
-    for (uint32_t g = tid; g < ngroups; g += MP_THREADS) {
-        const uint64_t e = (uint64_t)base + 4ull * g;
-        const uint4 c = ld_stream_v4(colind + e, pol_stream);
-        uint64_t vv[4];
-        ld_stream_v4_b64(vals + e, vv);
-        const uint32_t cc[4] = {c.x & colmask, c.y & colmask, c.z & colmask, c.w & colmask};
-        uint64_t xv[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) xv[k] = (e + k < nz1) ? load_x<PERSIST>(x, cc[k], pol_keep) : 0ull;
-#pragma unroll
-        for (int k = 0; k < 4; k++) sm.prod[4 * g + k] = Semi<DT>::mul(vv[k], xv[k]);
-    }
-    __syncthreads();
-
-    // (3) each thread walks MP_IPT merge items starting at its diagonal
-    const uint32_t diag = min((uint32_t)tid * MP_IPT, tile_items);
-    uint32_t lo = diag > tile_nnz ? diag - tile_nnz : 0u;
-    uint32_t hi = min(diag, tile_rows);
-    while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if (sm.rowend[mid] <= nz0 + (diag - mid - 1)) lo = mid + 1; else hi = mid;
-    }
-    uint32_t r = lo;                    // local row
-    uint32_t nz = nz0 + (diag - lo);    // absolute nz
-    const uint32_t first_row = r;
-    bool emitted = false;
-    uint64_t acc = 0;
-    uint32_t row_end = sm.rowend[r];
-#pragma unroll
-    for (int k = 0; k < MP_IPT; k++) {
-        if (diag + k < tile_items) {
-            if (nz < row_end) {
-                acc = Semi<DT>::add(acc, sm.prod[nz - base]);
-                nz++;
-            } else {
-                sm.yrow[r] = acc;
-                emitted = true;
-                acc = 0;
-                r++;
-                row_end = sm.rowend[r];
-            }
-        }
-    }
-    sm.crow[tid] = r;
-    sm.cval[tid] = acc;
-    __syncthreads();
-
-    // (4) the first row a thread completed may have begun in earlier threads: add their carries
-    if (emitted) {
-        int k = tid;
-        while (k > 0 && sm.crow[k - 1] == first_row) k--;
-        if (k < tid) {
-            uint64_t c = sm.cval[k];
-            for (int q = k + 1; q < tid; q++) c = Semi<DT>::add(c, sm.cval[q]);
-            sm.yrow[first_row] = Semi<DT>::add(c, sm.yrow[first_row]);
-        }
-    }
-    // tile carry-out: the partial of the row left open (threads whose walk ended in it)
-    if (tid == MP_THREADS - 1) {
-        const bool has_items = tile_rows > 0 ? (nz1 > sm.rowend[tile_rows - 1]) : (tile_nnz > 0);
-        int k = tid;
-        while (k > 0 && sm.crow[k - 1] == tile_rows) k--;
-        uint64_t c = sm.cval[k];
-        for (int q = k + 1; q <= tid; q++) c = Semi<DT>::add(c, sm.cval[q]);
-        carry_row[t] = has_items ? r1 : NO_ROW;
-        carry_val[t] = c;
-    }
-    __syncthreads();
-
-    // (5) coalesced write of the rows completed in this tile
-    for (uint32_t i = tid; i < tile_rows; i += MP_THREADS) {
-        uint64_t v = sm.yrow[i];
-        if (READ_Y) v = Semi<DT>::add(y[r0 + i], v);
-        y[r0 + i] = v;
-    }
-}
-
-// ---- merge-path SpMV v2: TMA-staged tile, register accumulation ----------------------------
-// One CTA per tile, like v1, but (a) the tile's column indices, values and row-end offsets are
-// brought into shared memory by three 1-D bulk async copies (TMA, cp.async.bulk) issued by one
-// thread and signalled on an mbarrier -- no LSU wavefronts and no registers are spent on the
-// streams, and with 6 CTAs resident per SM ~200 KB of stream data is in flight per SM;
-// (b) every thread resolves its MP_IPT merge items first (which are entries, which are row
-// ends), issues all its x gathers back to back, then accumulates in registers: products never
-// go through shared memory; (c) completed rows are stored straight to y.
-// The LSU is left to what bounds this kernel on a matrix without locality: one L2 sector
-// request per gathered x element (profiles/r01_gather_ceiling.txt).
-struct TmaSmem {
-    uint64_t val[MP_TILE + 8];
-    uint64_t cval[MP_THREADS];
-    uint32_t col[MP_TILE + 8];
-    uint32_t rowend[MP_TILE + 12];
-    uint32_t crow[MP_THREADS];
-    uint64_t mbar;
-};
-
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void tma_load_1d(void *dst_smem, const void *src, uint32_t bytes, uint64_t *mbar, uint64_t pol)
-{
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-        ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(mbar)), "l"(pol) : "memory");
-}
-
-template <int DT, bool PERSIST, bool READ_Y>
-__global__ void __launch_bounds__(MP_THREADS, 6)
-spmv_merge_tma_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restrict__ colind,
-                      const uint64_t *__restrict__ vals, const uint64_t *__restrict__ x,
-                      uint64_t *__restrict__ y, uint32_t rows, const uint32_t *__restrict__ tile_row,
-                      const uint32_t *__restrict__ tile_nz, uint32_t *__restrict__ carry_row,
-                      uint64_t *__restrict__ carry_val, uint32_t colmask)
-{
-    __shared__ __align__(128) TmaSmem sm;
-    const uint32_t t = blockIdx.x;
-    const int tid = threadIdx.x;
-    if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&sm.mbar)));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    const uint32_t r0 = __ldg(tile_row + t), r1 = __ldg(tile_row + t + 1);
-    const uint32_t nz0 = __ldg(tile_nz + t), nz1 = __ldg(tile_nz + t + 1);
-    const uint32_t tile_rows = r1 - r0, tile_nnz = nz1 - nz0;
-    const uint32_t tile_items = tile_rows + tile_nnz;
-    const uint32_t base = nz0 & ~3u;                       // 16-byte aligned start of the entry streams
-    const uint32_t cnt = (nz1 - base + 3u) & ~3u;          // entries copied (multiple of 4)
-    const uint32_t rbase = (r0 + 1u) & ~3u;                // rowptr[r0+1 .. r1+1] = row ends of rows r0..r1
-    const uint32_t rcnt = (r1 + 2u - rbase + 3u) & ~3u;
-    const uint32_t roff = r0 + 1u - rbase;
-    __syncthreads();
-    if (tid == 0) {
-        const uint64_t pol = policy_evict_first();
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&sm.mbar)),
-                     "r"(cnt * 12u + rcnt * 4u) : "memory");
-        tma_load_1d(sm.rowend, rowptr + rbase, rcnt * 4u, &sm.mbar, pol);
-        if (cnt) {
-            tma_load_1d(sm.col, colind + base, cnt * 4u, &sm.mbar, pol);
-            tma_load_1d(sm.val, vals + base, cnt * 8u, &sm.mbar, pol);
-        }
-    }
-    {   // wait for the three copies (phase 0)
-        uint32_t done = 0;
-        while (!done)
-            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
-                         : "=r"(done) : "r"(smem_u32(&sm.mbar)) : "memory");
-    }
-    const uint32_t *rowend = sm.rowend + roff;             // rowend[i] = end offset of local row i
-
-    // merge-path start of this thread inside the tile
-    const uint32_t diag = min((uint32_t)tid * MP_IPT, tile_items);
-    uint32_t lo = diag > tile_nnz ? diag - tile_nnz : 0u;
-    uint32_t hi = min(diag, tile_rows);
-    while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if (rowend[mid] <= nz0 + (diag - mid - 1)) lo = mid + 1; else hi = mid;
-    }
-    const uint32_t first_row = lo;
-    const uint32_t nz_first = nz0 + (diag - lo);
-    // pass 1: which of my items are row ends (bit k), how many are entries
-    uint32_t r = lo, nz = nz_first, ends = 0;
-    uint32_t row_end = rowend[r];
-#pragma unroll
-    for (int k = 0; k < MP_IPT; k++) {
-        if (diag + k < tile_items) {
-            if (nz < row_end) nz++;
-            else { ends |= 1u << k; r++; row_end = rowend[r]; }
-        }
-    }
-    // pass 2: all gathers in flight together.  Item k, when it is an entry, is my
-    // (k - #row-ends before k)-th entry.
-    const uint64_t pol_keep = policy_evict_last();
-    const uint32_t off = nz_first - base;
-    uint64_t xv[MP_IPT];
-#pragma unroll
-    for (int k = 0; k < MP_IPT; k++) {
-        const bool is_entry = (diag + k < tile_items) && !((ends >> k) & 1u);
-        const uint32_t jk = k - __popc(ends & ((1u << k) - 1u));
-        xv[k] = is_entry ? load_x<PERSIST>(x, sm.col[off + jk] & colmask, pol_keep) : 0ull;
-    }
-    // pass 3: accumulate in merge order
-    uint64_t acc = 0, first_val = 0;
-    bool emitted = false;
-    uint32_t rr = first_row;
-#pragma unroll
-    for (int k = 0; k < MP_IPT; k++) {
-        if (diag + k < tile_items) {
-            if ((ends >> k) & 1u) {
-                if (!emitted) { first_val = acc; emitted = true; }
-                else {
-                    uint64_t v = acc;
-                    if (READ_Y) v = Semi<DT>::add(y[r0 + rr], v);
-                    y[r0 + rr] = v;
-                }
-                acc = 0;
-                rr++;
-            } else {
-                const uint32_t jk = k - __popc(ends & ((1u << k) - 1u));
-                acc = Semi<DT>::add(acc, Semi<DT>::mul(sm.val[off + jk], xv[k]));
-            }
-        }
-    }
-    sm.crow[tid] = rr;
-    sm.cval[tid] = acc;
-    __syncthreads();
-
-    if (emitted) {  // my first completed row may have begun in earlier threads
-        int k = tid;
-        while (k > 0 && sm.crow[k - 1] == first_row) k--;
-        uint64_t v = first_val;
-        if (k < tid) {
-            uint64_t c = sm.cval[k];
-            for (int q = k + 1; q < tid; q++) c = Semi<DT>::add(c, sm.cval[q]);
-            v = Semi<DT>::add(c, v);
-        }
-        if (READ_Y) v = Semi<DT>::add(y[r0 + first_row], v);
-        y[r0 + first_row] = v;
-    }
-    if (tid == MP_THREADS - 1) {  // tile carry-out: partial of the row left open
-        const bool has_items = tile_rows > 0 ? (nz1 > rowend[tile_rows - 1]) : (tile_nnz > 0);
-        int k = tid;
-        while (k > 0 && sm.crow[k - 1] == tile_rows) k--;
-        uint64_t c = sm.cval[k];
-        for (int q = k + 1; q <= tid; q++) c = Semi<DT>::add(c, sm.cval[q]);
-        carry_row[t] = has_items ? r1 : NO_ROW;
-        carry_val[t] = c;
-    }
 }
 
 // ---- kernel 3: flagged segmented sum -------------------------------------------------------
@@ -358,7 +75,6 @@ __device__ __forceinline__ void store_segment(uint64_t *__restrict__ y, const ui
         y[row] = v;
     }
 }
-
 // EPT = consecutive entries per thread (8 or 16); the tile is always B2_FLAG_TILE entries, so the
 // CTA has B2_FLAG_TILE / EPT threads.
 template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, int EPT>
@@ -518,321 +234,139 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
         carry_val[t] = out;
     }
 }
-
-// ---- kernel 4: persistent flagged segmented sum with a TMA-fed shared-memory ring ------------------
-// Same arithmetic and the same flagged tiles as kernel 3, but the CTAs are persistent (grid = SMs x
-// resident CTAs, tiles dealt round-robin) and the two entry streams of tile i + RING are brought into
-// a shared-memory ring by 1-D bulk async copies (TMA, cp.async.bulk -> UBLKCP) issued by one thread
-// as soon as the ring slot has been read into registers.  What bounds this kernel on a matrix without
-// locality is the rate at which one SM can post L2 requests for the x gathers (ncu:
-// l1tex__m_l1tex2xbar_req_cycles_active, profiles/r01_k3_flag_ncu_summary.txt); kernel 3 leaves that
-// port idle while a fresh CTA waits for its first HBM loads, here the streams are already on chip
-// when a tile starts, so the gathers are issued back to back.
-constexpr int PK_RING = 2;
-constexpr uint32_t PK_STAGE_BYTES = B2_FLAG_TILE * 12u;
-constexpr uint32_t PK_SMEM_BYTES = PK_RING * PK_STAGE_BYTES + 128;  // + full[RING], empty[RING] mbarriers
-
-template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY>
-__global__ void __launch_bounds__(B2_FLAG_TILE / 8, 4)
-spmv_flag_ring_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
-                      const uint64_t *__restrict__ x, uint64_t *__restrict__ y,
-                      const uint32_t *__restrict__ seg_row, uint32_t rows, const uint32_t *__restrict__ tile_seg,
-                      uint32_t *__restrict__ carry_row, uint64_t *__restrict__ carry_val, uint32_t ntiles)
-{
-    constexpr int EPT = 8, THREADS = B2_FLAG_TILE / EPT, WARPS = THREADS / 32;
-    extern __shared__ __align__(128) unsigned char pk_smem[];
-    // slot s: values at s*PK_STAGE_BYTES (16 KB), column indices behind them (8 KB)
-    uint64_t *s_bar = reinterpret_cast<uint64_t *>(pk_smem + PK_RING * PK_STAGE_BYTES);
-    __shared__ uint32_t s_wcnt[WARPS];
-    __shared__ uint32_t s_wflag[WARPS];
-    __shared__ uint64_t s_wsum[WARPS];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint64_t pol_stream = policy_evict_first(), pol_keep = policy_evict_last();
-
-    if (tid == 0) {
-#pragma unroll
-        for (int s = 0; s < PK_RING; s++) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[s])));            // full: producer + tx bytes
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&s_bar[PK_RING + s])), "r"(WARPS));  // empty: one arrival per warp
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-#pragma unroll
-        for (int s = 0; s < PK_RING; s++) {
-            const uint64_t t = (uint64_t)blockIdx.x + (uint64_t)s * gridDim.x;
-            if (t < ntiles) {
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&s_bar[s])), "r"(PK_STAGE_BYTES) : "memory");
-                tma_load_1d(pk_smem + s * PK_STAGE_BYTES, vals + t * B2_FLAG_TILE, B2_FLAG_TILE * 8u, &s_bar[s], pol_stream);
-                tma_load_1d(pk_smem + s * PK_STAGE_BYTES + B2_FLAG_TILE * 8u, colind + t * B2_FLAG_TILE, B2_FLAG_TILE * 4u, &s_bar[s], pol_stream);
-            }
-        }
-    }
-    __syncthreads();
-
-    uint32_t it = 0;
-    for (uint64_t t64 = blockIdx.x; t64 < ntiles; t64 += gridDim.x, it++) {
-        const uint32_t t = (uint32_t)t64;
-        const int slot = it % PK_RING;
-        const uint32_t parity = (it / PK_RING) & 1u;
-        const uint32_t tseg = __ldg(tile_seg + t);
-        {
-            uint32_t done = 0;
-            while (!done)
-                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                             : "=r"(done) : "r"(smem_u32(&s_bar[slot])), "r"(parity) : "memory");
-        }
-        uint32_t c[EPT];
-        uint64_t p[EPT];
-        {
-            const uint4 *sc = reinterpret_cast<const uint4 *>(pk_smem + slot * PK_STAGE_BYTES + B2_FLAG_TILE * 8u) + tid * 2;
-            const uint4 c0 = sc[0], c1 = sc[1];
-            c[0] = c0.x; c[1] = c0.y; c[2] = c0.z; c[3] = c0.w; c[4] = c1.x; c[5] = c1.y; c[6] = c1.z; c[7] = c1.w;
-        }
-        uint64_t xv[EPT];
-#pragma unroll
-        for (int i = 0; i < EPT; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
-        {
-            const ulonglong2 *sv = reinterpret_cast<const ulonglong2 *>(pk_smem + slot * PK_STAGE_BYTES) + tid * 4;
-#pragma unroll
-            for (int g = 0; g < 4; g++) { const ulonglong2 v = sv[g]; p[2 * g] = v.x; p[2 * g + 1] = v.y; }
-        }
-        // release the slot: my reads (generic proxy) are ordered before the refill (async proxy) that
-        // thread 0 issues once every warp has arrived.  (A __syncthreads is not enough here: BAR.SYNC
-        // defers its blocking to the next instruction that touches shared memory, and the bulk copy
-        // is not one.)
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_bar[PK_RING + slot])) : "memory");
-
-        uint32_t f = 0;
-#pragma unroll
-        for (int i = 0; i < EPT; i++) f |= (c[i] >> 31) << i;
-        const uint32_t nfl = __popc(f);
-        const uint32_t lt = (1u << lane) - 1u;
-        uint32_t lane_prefix = 0, warp_flags = 0;
-#pragma unroll
-        for (int bit = 0; (1 << bit) <= EPT; bit++) {
-            const uint32_t bal_b = __ballot_sync(0xffffffffu, (nfl >> bit) & 1u);
-            lane_prefix += __popc(bal_b & lt) << bit;
-            warp_flags += __popc(bal_b) << bit;
-        }
-        const uint32_t bal = __ballot_sync(0xffffffffu, nfl != 0);
-        if (lane == 31) s_wcnt[warp] = warp_flags;
-        __syncthreads();  // (A)
-        if (tid == 0) {
-            const uint64_t tn = t64 + (uint64_t)PK_RING * gridDim.x;
-            if (tn < ntiles) {
-                uint32_t done = 0;  // every warp holds its part of the slot in registers
-                while (!done)
-                    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                                 : "=r"(done) : "r"(smem_u32(&s_bar[PK_RING + slot])), "r"(parity) : "memory");
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&s_bar[slot])), "r"(PK_STAGE_BYTES) : "memory");
-                tma_load_1d(pk_smem + slot * PK_STAGE_BYTES, vals + tn * B2_FLAG_TILE, B2_FLAG_TILE * 8u, &s_bar[slot], pol_stream);
-                tma_load_1d(pk_smem + slot * PK_STAGE_BYTES + B2_FLAG_TILE * 8u, colind + tn * B2_FLAG_TILE, B2_FLAG_TILE * 4u, &s_bar[slot], pol_stream);
-            }
-        }
-        uint32_t segs_before = tseg + lane_prefix, tile_flags = 0;
-#pragma unroll
-        for (int w = 0; w < WARPS; w++) {
-            const uint32_t n = s_wcnt[w];
-            if (w < warp) segs_before += n;
-            tile_flags += n;
-        }
-        uint32_t close_row = NO_ROW;
-        uint64_t y_old = 0;
-        if (nfl != 0 && segs_before != 0) {
-            close_row = HAS_EMPTY ? __ldg(seg_row + segs_before - 1) : segs_before - 1;
-            if (close_row >= rows) close_row = NO_ROW;
-            if (READ_Y && close_row != NO_ROW) y_old = y[close_row];
-        }
-
-        uint64_t acc = 0, head = 0;
-        uint32_t seen = 0;
-#pragma unroll
-        for (int i = 0; i < EPT; i++) {
-            p[i] = Semi<DT>::mul(p[i], xv[i]);
-            const uint32_t fl = (f >> i) & 1u;
-            head = (fl & ~seen & 1u) ? acc : head;
-            seen |= fl;
-            acc = fl ? 0ull : acc;
-            acc = Semi<DT>::add(acc, p[i]);
-        }
-        const uint32_t below = bal & ((2u << lane) - 1u);
-        const int start = below ? 31 - __clz(below) : 0;
-        uint64_t S = acc;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
-            if (lane - d >= start) S = Semi<DT>::add(n, S);
-        }
-        uint64_t carry_in = __shfl_up_sync(0xffffffffu, S, 1);
-        if (lane == 0) carry_in = 0;
-        const bool open_left = (bal & lt) == 0;
-        if (lane == 31) { s_wsum[warp] = S; s_wflag[warp] = bal != 0; }
-        __syncthreads();  // (B)
-
-        uint64_t cw = 0;
-        if (warp > 0) {
-            int w0 = warp - 1;
-            while (w0 > 0 && !s_wflag[w0]) w0--;
-            cw = s_wsum[w0];
-            for (int w = w0 + 1; w < warp; w++) cw = Semi<DT>::add(cw, s_wsum[w]);
-        }
-        if (nfl != 0) {
-            if (close_row != NO_ROW) {
-                uint64_t val = open_left ? Semi<DT>::add(cw, carry_in) : carry_in;
-                val = Semi<DT>::add(val, head);
-                if (READ_Y) val = Semi<DT>::add(y_old, val);
-                y[close_row] = val;
-            }
-            if (nfl > 1) {
-                uint64_t a = 0;
-                uint32_t k = 0;
-#pragma unroll
-                for (int i = 0; i < EPT; i++) {
-                    if ((f >> i) & 1u) {
-                        if (k != 0) store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before + k - 1, a);
-                        k++;
-                        a = 0;
-                    }
-                    a = Semi<DT>::add(a, p[i]);
-                }
-            }
-        }
-        if (tid == THREADS - 1) {
-            const uint64_t out = bal ? S : Semi<DT>::add(cw, S);
-            const uint32_t seg_total = tseg + tile_flags;
-            uint32_t row = NO_ROW;
-            if (seg_total != 0) {
-                row = HAS_EMPTY ? __ldg(seg_row + seg_total - 1) : seg_total - 1;
-                if (row >= rows) row = NO_ROW;
-            }
-            carry_row[t] = row;
-            carry_val[t] = out;
-        }
-        // s_wcnt is rewritten before (A) of the next tile and was last read before (B) of this one;
-        // s_wsum / s_wflag are rewritten after (A) of the next tile, which every reader above has passed
-    }
-}
-
-// ---- kernel 5: flagged segmented sum with WARP-sized tiles ------------------------------------------
-// Same flagged streams as kernel 3, but the unit of work is one warp = 256 consecutive entries, and
-// warps never talk to each other: no shared memory, no __syncthreads.  The number of row-start flags
-// before each warp's first entry comes from a table built at setup (warp_seg, 4 bytes per 256 entries),
-// rows that straddle warps go through the carry arrays (one slot per warp) and spmv_fixup_kernel.
-// Why: on a matrix without locality the x gathers queue in the SM's single in-order load pipeline at
-// ~1 wavefront / clk, and every shared-memory round trip or barrier of kernel 3 waits behind that
-// queue once more (ncu: short_scoreboard + barrier + mio stalls = 45 % in
-// profiles/r01_k3_flag_ncu_summary.txt).  Here the only dependent round trips of a warp are
-// streams -> gathers (-> seg_row -> y when the slab has empty rows / accumulates), and the 32 warps
-// resident on an SM are 32 independent chains, so the load pipeline does not run dry.
-constexpr int WK_ENTRIES = 256;  // per warp: 32 lanes x 8 entries
+// ---- kernel 6: flagged segmented sum by persistent, autonomous warps ---------------------------
+// Same flagged format and the same per-thread arithmetic as kernel 3 (8 consecutive entries per thread,
+// 256 per warp step), but:
+//   * a warp owns a CONTIGUOUS chunk of the slab's entry stream and loops over it, so the row left open at
+//     the end of a step stays in a register (wcarry) and the flag count before the next step is a running
+//     sum: no tile_seg / warp_seg lookups after the first, and one carry per CHUNK for the fix-up pass
+//     instead of one per tile;
+//   * the 12 B/entry streams of step i+1 are requested before the x gathers of step i are issued (register
+//     double buffer; optionally the TMA unit also pulls step i+pf into L2), so every warp always has 3 KB of
+//     HBM reads in flight.  A non-persistent CTA spends most of its life NOT loading streams (launch, gather
+//     round trip, row logic, y round trip, exit), which is what held kernel 3 near 200 GNNZ/s whatever the
+//     gather locality;
+//   * no shared memory and no block barrier: the warps of an SM are independent chains;
+//   * accumulating launches (y += ..., and every slab after the first) add their row sums with a reduction
+//     at L2 (red.global.add) instead of load / add / store: one request instead of two and no y round trip.
+constexpr int SK_THREADS = 256;
+constexpr int WK_ENTRIES = 256;  // per warp step: 32 lanes x 8 entries
 constexpr int WK_PER_TILE = (int)(B2_FLAG_TILE / WK_ENTRIES);
 
-// ABL (measurement only, option "ablate"): 0 = the kernel; 1 = results kept in registers, no y / carry
-// stores; 2 = also no segmented scan; 3 = no row logic at all (streams + gathers + multiply-add)
-template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, int ABL>
-__global__ void __launch_bounds__(256, 4)
-spmv_flag_warp_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
-                      const uint64_t *__restrict__ x, uint64_t *__restrict__ y,
-                      const uint32_t *__restrict__ seg_row, uint32_t rows, const uint32_t *__restrict__ warp_seg,
-                      uint32_t *__restrict__ carry_row, uint64_t *__restrict__ carry_val, uint32_t nwarps)
+#ifndef B200SPMV_ABLATE
+#define B200SPMV_ABLATE 0  // measurement builds only (make ablate): 1 no y stores, 2 no scan, 3 no row logic, 4 no gathers
+#endif
+
+// y[row] (+)= v.  Each row is closed by exactly one thread of a launch, so the reduction meets no contention and
+// gives the same single rounded addition y_old + v a load / add / store would.
+template <int DT, bool READ_Y>
+__device__ __forceinline__ void emit_row(uint64_t *__restrict__ y, uint32_t row, uint64_t v)
 {
-    constexpr int EPT = 8;
-    const int lane = threadIdx.x & 31;
-    const uint32_t gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (gw >= nwarps) return;
-    const uint64_t pos = (uint64_t)gw * WK_ENTRIES + (uint64_t)lane * EPT;
+    if (!READ_Y) { y[row] = v; return; }
+    if (DT == B200SPMV_F64)
+        asm volatile("red.global.add.f64 [%0], %1;" ::"l"(y + row), "d"(__longlong_as_double((long long)v)) : "memory");
+    else
+        asm volatile("red.global.add.u64 [%0], %1;" ::"l"(y + row), "l"(v) : "memory");
+}
 
-    uint32_t c[EPT];
-    uint64_t p[EPT];
-    ld256_u32(colind + pos, c);
-    ld256_u64(vals + pos, p);
-    ld256_u64(vals + pos + 4, p + 4);
-    const uint32_t wbase = __ldg(warp_seg + gw);
-    const uint64_t pol_keep = policy_evict_last();
-    uint64_t xv[EPT];
+__device__ __forceinline__ void stream_load(uint32_t (&c)[8], uint64_t (&p)[8], const uint32_t *cp, const uint64_t *vp)
+{
+    ld256_u32(cp, c);
+    ld256_u64(vp, p);
+    ld256_u64(vp + 4, p + 4);
+}
+
+// One warp step: 256 consecutive entries, c / p = this lane's 8 column ids (flag in bit 31) and values.
+// segs_base = row-start flags before the step's first entry, wcarry = partial sum of the row open on entry;
+// both are advanced to the end of the step.
+template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY>
+__device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p)[8], const uint64_t *__restrict__ x,
+                                            uint64_t *__restrict__ y, const uint32_t *__restrict__ seg_row, uint32_t rows,
+                                            int lane, uint32_t lt, uint64_t pol_keep, uint32_t &segs_base, uint64_t &wcarry)
+{
+    constexpr int ABL = B200SPMV_ABLATE;
+    uint64_t xv[8];
 #pragma unroll
-    for (int i = 0; i < EPT; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
-
-    if (ABL == 3) {
+    for (int i = 0; i < 8; i++) xv[i] = ABL >= 4 ? (uint64_t)c[i] : load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
+    if (ABL >= 3) {
         uint64_t a = 0;
 #pragma unroll
-        for (int i = 0; i < EPT; i++) a = Semi<DT>::add(a, Semi<DT>::mul(p[i], xv[i]));
-        if (a == 0x123456789abcdefull) y[0] = a + wbase;
+        for (int i = 0; i < 8; i++) a = Semi<DT>::add(a, Semi<DT>::mul(p[i], xv[i]));
+        wcarry ^= a;
         return;
     }
     uint32_t f = 0;
 #pragma unroll
-    for (int i = 0; i < EPT; i++) f |= (c[i] >> 31) << i;
+    for (int i = 0; i < 8; i++) f |= (c[i] >> 31) << i;
     const uint32_t nfl = __popc(f);
-    const uint32_t lt = (1u << lane) - 1u;
+    // flags in lower lanes: sum over the bits of nfl of ballots (no dependent shuffle chain)
     uint32_t lane_prefix = 0, warp_flags = 0;
 #pragma unroll
-    for (int bit = 0; (1 << bit) <= EPT; bit++) {
+    for (int bit = 0; bit < 4; bit++) {
         const uint32_t bal_b = __ballot_sync(0xffffffffu, (nfl >> bit) & 1u);
         lane_prefix += __popc(bal_b & lt) << bit;
         warp_flags += __popc(bal_b) << bit;
     }
     const uint32_t bal = __ballot_sync(0xffffffffu, nfl != 0);
-    const uint32_t segs_before = wbase + lane_prefix;
-    // the row my first flag closes and (accumulate / later slabs) its current y: issued while the
-    // gathers are in flight
+    const uint32_t segs_before = segs_base + lane_prefix;
+    // the row my first flag closes (its id is looked up while the gathers are in flight)
     uint32_t close_row = NO_ROW;
-    uint64_t y_old = 0;
     if (nfl != 0 && segs_before != 0) {
         close_row = HAS_EMPTY ? __ldg(seg_row + segs_before - 1) : segs_before - 1;
         if (close_row >= rows) close_row = NO_ROW;
-        if (READ_Y && close_row != NO_ROW) y_old = y[close_row];
     }
-
+    // branch-free sequential pass: head = sum before my first flag, acc = sum after my last flag
+    const uint32_t f1 = f & (0u - f);
     uint64_t acc = 0, head = 0;
-    uint32_t seen = 0;
 #pragma unroll
-    for (int i = 0; i < EPT; i++) {
+    for (int i = 0; i < 8; i++) {
         p[i] = Semi<DT>::mul(p[i], xv[i]);
-        const uint32_t fl = (f >> i) & 1u;
-        head = (fl & ~seen & 1u) ? acc : head;
-        seen |= fl;
-        acc = fl ? 0ull : acc;
+        head = ((f1 >> i) & 1u) ? acc : head;
+        acc = ((f >> i) & 1u) ? 0ull : acc;
         acc = Semi<DT>::add(acc, p[i]);
     }
-    // segmented inclusive scan of the open tails: S = sum from the nearest flagged lane at or below me
+    // segmented inclusive scan of the open tails over the warp: S = sum of tails from the nearest flagged lane at
+    // or below me (or lane 0) to me.  Steps longer than the warp's longest open run change nothing: skipped.
     const uint32_t below = bal & ((2u << lane) - 1u);
     const int start = below ? 31 - __clz(below) : 0;
     uint64_t S = acc;
-    uint64_t carry_in = 0;
     if (ABL < 2) {
+        const int span = __reduce_max_sync(0xffffffffu, lane - start);
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
+            if (d > span) break;
             const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
             if (lane - d >= start) S = Semi<DT>::add(n, S);
         }
-        carry_in = __shfl_up_sync(0xffffffffu, S, 1);
-        if (lane == 0) carry_in = 0;
     }
+    uint64_t prev = __shfl_up_sync(0xffffffffu, S, 1);  // open partial that ends at lane - 1
+    if (lane == 0) prev = 0;
+    const uint64_t s31 = __shfl_sync(0xffffffffu, S, 31);
     if (ABL >= 1) {
-        uint64_t a = Semi<DT>::add(Semi<DT>::add(S, carry_in), Semi<DT>::add(head, y_old));
+        uint64_t a = Semi<DT>::add(prev, head) ^ (uint64_t)close_row;
 #pragma unroll
-        for (int i = 0; i < EPT; i++) a ^= p[i];
-        if (a == 0x123456789abcdefull) y[close_row & 1023] = a + start;
+        for (int i = 0; i < 8; i++) a ^= p[i];
+        wcarry ^= a ^ s31;
+        segs_base += warp_flags;
         return;
     }
-
     if (nfl != 0) {
         if (close_row != NO_ROW) {
-            // when no lane below me has a flag this is only the warp's share of the row: the shares of
-            // the preceding warps arrive through their carries
-            uint64_t val = Semi<DT>::add(carry_in, head);
-            if (READ_Y) val = Semi<DT>::add(y_old, val);
-            y[close_row] = val;
+            // no flagged lane below me: the row was open when the step began, its earlier part is wcarry
+            uint64_t val = (bal & lt) == 0 ? Semi<DT>::add(wcarry, prev) : prev;
+            val = Semi<DT>::add(val, head);
+            emit_row<DT, READ_Y>(y, close_row, val);
         }
-        if (nfl > 1) {
+        if (nfl > 1) {  // rows that begin and end inside my 8 entries
             uint64_t a = 0;
             uint32_t k = 0;
 #pragma unroll
-            for (int i = 0; i < EPT; i++) {
+            for (int i = 0; i < 8; i++) {
                 if ((f >> i) & 1u) {
-                    if (k != 0) store_segment<DT, READ_Y, HAS_EMPTY>(y, seg_row, rows, segs_before + k - 1, a);
+                    if (k != 0) {
+                        const uint32_t row = HAS_EMPTY ? __ldg(seg_row + segs_before + k - 1) : segs_before + k - 1;
+                        if (row < rows) emit_row<DT, READ_Y>(y, row, a);
+                    }
                     k++;
                     a = 0;
                 }
@@ -840,15 +374,77 @@ spmv_flag_warp_kernel(const uint32_t *__restrict__ colind, const uint64_t *__res
             }
         }
     }
-    if (lane == 31) {  // carry-out: the row left open at the end of this warp's entries
-        const uint32_t seg_total = wbase + warp_flags;
-        uint32_t row = NO_ROW;
-        if (seg_total != 0) {
-            row = HAS_EMPTY ? __ldg(seg_row + seg_total - 1) : seg_total - 1;
-            if (row >= rows) row = NO_ROW;
+    wcarry = bal ? s31 : Semi<DT>::add(wcarry, s31);
+    segs_base += warp_flags;
+}
+
+// nwt = warp steps (256 entries) of the slab, cut into nchunks chunks of `chunk` steps; warp w of the grid takes
+// chunks w, w + warps, ...  DB: register double buffer for the streams.  pf_dist: L2 bulk prefetch distance in
+// steps (0 = off).
+template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, bool DB>
+__global__ void __launch_bounds__(SK_THREADS, DB ? 2 : 3)
+spmv_stream_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
+                   const uint64_t *__restrict__ x, uint64_t *__restrict__ y, const uint32_t *__restrict__ seg_row,
+                   uint32_t rows, const uint32_t *__restrict__ warp_seg, uint32_t *__restrict__ carry_row,
+                   uint64_t *__restrict__ carry_val, uint32_t nwt, uint32_t chunk, uint32_t nchunks, uint32_t pf_dist)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint64_t pol_keep = policy_evict_last();
+    const uint32_t nwarps = gridDim.x * (SK_THREADS / 32);
+#define B2_STREAM_PREFETCH()                                                                                              \
+    if (pf_dist != 0 && lane == 0 && t + pf_dist < t1) {                                                                  \
+        const uint64_t e = (uint64_t)(t + pf_dist) * WK_ENTRIES;                                                          \
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vals + e), "r"(WK_ENTRIES * 8u) : "memory");      \
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(colind + e), "r"(WK_ENTRIES * 4u) : "memory");    \
+    }
+#define B2_STREAM_STEP(C, P) \
+    stream_step<DT, PERSIST, READ_Y, HAS_EMPTY>(C, P, x, y, seg_row, rows, lane, lt, pol_keep, segs_base, wcarry)
+    for (uint32_t vc = blockIdx.x * (SK_THREADS / 32) + (threadIdx.x >> 5); vc < nchunks; vc += nwarps) {
+        uint32_t t = vc * chunk;
+        const uint32_t t1 = min(t + chunk, nwt);
+        uint32_t segs_base = __ldg(warp_seg + t);
+        uint64_t wcarry = 0;
+        const uint32_t *cp = colind + (uint64_t)t * WK_ENTRIES + lane * 8;
+        const uint64_t *vp = vals + (uint64_t)t * WK_ENTRIES + lane * 8;
+        uint32_t ca[8];
+        uint64_t pa[8];
+        stream_load(ca, pa, cp, vp);
+        if (DB) {
+            uint32_t cb[8];
+            uint64_t pb[8];
+            while (true) {
+                if (t + 1 < t1) stream_load(cb, pb, cp + WK_ENTRIES, vp + WK_ENTRIES);
+                B2_STREAM_PREFETCH();
+                B2_STREAM_STEP(ca, pa);
+                if (++t >= t1) break;
+                cp += WK_ENTRIES; vp += WK_ENTRIES;
+                if (t + 1 < t1) stream_load(ca, pa, cp + WK_ENTRIES, vp + WK_ENTRIES);
+                B2_STREAM_PREFETCH();
+                B2_STREAM_STEP(cb, pb);
+                if (++t >= t1) break;
+                cp += WK_ENTRIES; vp += WK_ENTRIES;
+            }
+        } else {
+            while (true) {
+                B2_STREAM_PREFETCH();
+                B2_STREAM_STEP(ca, pa);
+                if (++t >= t1) break;
+                cp += WK_ENTRIES; vp += WK_ENTRIES;
+                stream_load(ca, pa, cp, vp);
+            }
         }
-        carry_row[gw] = row;
-        carry_val[gw] = S;
+#undef B2_STREAM_STEP
+#undef B2_STREAM_PREFETCH
+        if (lane == 0) {  // carry-out: the row left open at the end of the chunk
+            uint32_t row = NO_ROW;
+            if (B200SPMV_ABLATE == 0 && segs_base != 0) {
+                row = HAS_EMPTY ? __ldg(seg_row + segs_base - 1) : segs_base - 1;
+                if (row >= rows) row = NO_ROW;
+            }
+            carry_row[vc] = row;
+            carry_val[vc] = wcarry;
+        }
     }
 }
 
@@ -972,45 +568,6 @@ spmv_rowseq_kernel(const uint32_t *__restrict__ rowptr, const uint32_t *__restri
 
 // ---- host side -----------------------------------------------------------------------------
 
-// Merge-path tile tables for every slab.  Slab s owns tile-table entries
-// [h_tile_base[s] + s, h_tile_base[s+1] + s] (ntiles_s + 1 of them) and carries [h_tile_base[s], ..).
-int b2_build_tiles(b200spmv_ctx *ctx)
-{
-    DeviceCsr &m = ctx->csr;
-    b2_free(m.tile_row); b2_free(m.tile_nz); b2_free(m.carry_row);
-    { uint64_t *cv = (uint64_t *)m.carry_val; b2_free(cv); m.carry_val = nullptr; }
-    std::vector<uint32_t> h_ptr(2 * (size_t)ctx->slabs);
-    const size_t stride = ctx->rowptr_stride;
-    uint32_t total = 0;
-    for (int s = 0; s < ctx->slabs; s++) {
-        uint32_t b = 0, e = 0;
-        B2_CHECK(ctx, cudaMemcpyAsync(&b, m.rowptr + s * stride, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        B2_CHECK(ctx, cudaMemcpyAsync(&e, m.rowptr + s * stride + ctx->local_rows, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        B2_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-        const uint64_t items = (uint64_t)ctx->local_rows + (e - b);
-        ctx->h_tile_base[s] = total;
-        total += b2_div_up(items, MP_TILE);
-    }
-    ctx->h_tile_base[ctx->slabs] = total;
-    ctx->total_tiles = total;
-    B2_TRY(b2_alloc(ctx, &m.tile_row, (size_t)total + ctx->slabs));
-    B2_TRY(b2_alloc(ctx, &m.tile_nz, (size_t)total + ctx->slabs));
-    B2_TRY(b2_alloc(ctx, &m.carry_row, (size_t)total + 1));
-    uint64_t *cv = nullptr;
-    B2_TRY(b2_alloc(ctx, &cv, (size_t)total + 1));
-    m.carry_val = cv;
-    for (int s = 0; s < ctx->slabs; s++) {
-        const uint32_t nt = ctx->h_tile_base[s + 1] - ctx->h_tile_base[s];
-        tile_search_kernel<<<b2_div_up((uint64_t)nt + 1, 256), 256, 0, ctx->stream>>>(
-            m.rowptr + s * stride, ctx->local_rows, nt, m.tile_row + ctx->h_tile_base[s] + s,
-            m.tile_nz + ctx->h_tile_base[s] + s);
-        B2_CHECK(ctx, cudaGetLastError());
-    }
-    B2_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    return 0;
-}
-
-// Flagged format for kernel 3 (needs bit 31 of the column ids free).
 // longest row piece of a slab: the thread-per-row kernel is only chosen when no thread gets a long one
 __global__ void max_rowlen_kernel(const uint32_t *__restrict__ rowptr, uint32_t rows, uint32_t *__restrict__ out)
 {
@@ -1040,14 +597,18 @@ __global__ void chunk_rows_kernel(const uint32_t *__restrict__ tile_seg, const u
     out_row[k] = r;
 }
 
+// Flagged format for kernels 3 and 6 (needs bit 31 of the column ids free; otherwise only the row-sequential
+// kernel runs).
 int b2_build_flags(b200spmv_ctx *ctx)
 {
     DeviceCsr &m = ctx->csr;
     cudaStream_t s = ctx->stream;
-    b2_free(m.seg_row); b2_free(m.tile_seg); b2_free(m.warp_seg);
+    b2_free(m.seg_row); b2_free(m.tile_seg); b2_free(m.warp_seg); b2_free(m.carry_row);
+    { uint64_t *cv = (uint64_t *)m.carry_val; b2_free(cv); m.carry_val = nullptr; }
     ctx->flagged = false;
     ctx->colmask = 0xFFFFFFFFu;
-    if (ctx->cols > 0x80000000u || ctx->local_rows == 0) return 0;  // kernels 1/2 only
+    ctx->total_tiles = 0;
+    if (ctx->cols > 0x80000000u || ctx->local_rows == 0) return 0;
     const uint32_t rows = ctx->local_rows;
     const size_t stride = ctx->rowptr_stride;
     uint32_t total = 0;
@@ -1056,17 +617,13 @@ int b2_build_flags(b200spmv_ctx *ctx)
         total += (uint32_t)((ctx->h_slab_off[sl + 1] - ctx->h_slab_off[sl]) / B2_FLAG_TILE);
     }
     ctx->h_ftile_base[ctx->slabs] = total;
+    ctx->total_tiles = total;
     B2_TRY(b2_alloc(ctx, &m.seg_row, stride * ctx->slabs));
     B2_TRY(b2_alloc(ctx, &m.tile_seg, (size_t)total + ctx->slabs));
     B2_TRY(b2_alloc(ctx, &m.warp_seg, (size_t)total * WK_PER_TILE + ctx->slabs));
-    if ((uint64_t)total * WK_PER_TILE > ctx->total_tiles) {  // the carry arrays serve every kernel: one slot per warp tile
-        b2_free(m.carry_row);
-        { uint64_t *cv = (uint64_t *)m.carry_val; b2_free(cv); m.carry_val = nullptr; }
-        B2_TRY(b2_alloc(ctx, &m.carry_row, (size_t)total * WK_PER_TILE + 1));
-        uint64_t *cv = nullptr;
-        B2_TRY(b2_alloc(ctx, &cv, (size_t)total * WK_PER_TILE + 1));
-        m.carry_val = cv;
-    }
+    // carries: one slot per 256-entry warp step serves every kernel (kernel 3 uses one per tile, kernel 6 one per chunk)
+    B2_TRY(b2_alloc(ctx, &m.carry_row, (size_t)total * WK_PER_TILE + 1));
+    { uint64_t *cv = nullptr; B2_TRY(b2_alloc(ctx, &cv, (size_t)total * WK_PER_TILE + 1)); m.carry_val = cv; }
     uint32_t *segidx = nullptr;
     B2_TRY(b2_alloc(ctx, &segidx, (size_t)rows + 4));
     int rc = 0;
@@ -1116,17 +673,18 @@ int b2_build_flags(b200spmv_ctx *ctx)
     return 0;
 }
 
-// Will b2_spmv_launch cut the last slab's kernel into row chunks (and record ev_rowchunk[])?  Kernel 3 on the
-// flagged layout only: its tiles are consecutive pieces of the entry stream, hence of the rows.
 static bool dcsr_slab(const b200spmv_ctx *ctx, int sl)
 {
     const uint32_t nseg = ctx->h_nseg[sl];
     return ctx->opt_dcsr_x16 > 0 && nseg > 0 && (uint64_t)ctx->h_slab_nnz[sl] * 16 < (uint64_t)nseg * ctx->opt_dcsr_x16 &&
            ctx->h_maxrow[sl] <= (uint32_t)ctx->opt_dcsr_maxrow;
 }
+// Will b2_spmv_launch cut the last slab's kernel into row chunks (and record ev_rowchunk[])?  The flagged layout
+// only: the tiles of kernel 3 are consecutive pieces of the entry stream, hence of the rows (whichever of kernels
+// 3 and 6 is selected, the chunked last slab of b200spmv_exec runs kernel 3).
 bool b2_last_slab_chunkable(const b200spmv_ctx *ctx, int flags)
 {
-    return ctx->chunks_ready && ctx->flagged && ctx->opt_kernel == 3 && !(flags & B200SPMV_STRICT_ORDER) &&
+    return ctx->chunks_ready && ctx->flagged && !(flags & B200SPMV_STRICT_ORDER) &&
            ctx->order_n == 0 && ctx->local_rows > 0 && !dcsr_slab(ctx, ctx->slabs - 1);
 }
 
@@ -1168,11 +726,36 @@ __global__ void x_prefetch_kernel(const char *base, uint64_t bytes)
     }
 }
 
+// template dispatch over the three run-time booleans (PERSIST, READ_Y, HAS_EMPTY)
+#define B2_DISPATCH3(p, r, e, CALL)                                      \
+    do {                                                                 \
+        if (p) {                                                         \
+            if (r) { if (e) CALL(true, true, true); else CALL(true, true, false); }      \
+            else { if (e) CALL(true, false, true); else CALL(true, false, false); }      \
+        } else {                                                         \
+            if (r) { if (e) CALL(false, true, true); else CALL(false, true, false); }    \
+            else { if (e) CALL(false, false, true); else CALL(false, false, false); }    \
+        }                                                                \
+    } while (0)
+
+static bool prof_begin(b200spmv_ctx *ctx, cudaStream_t s)
+{
+    if (!ctx->opt_profile || ctx->prof_n + 2 > 128) return false;
+    if (!ctx->prof_ev[ctx->prof_n]) { cudaEventCreate(&ctx->prof_ev[ctx->prof_n]); cudaEventCreate(&ctx->prof_ev[ctx->prof_n + 1]); }
+    cudaEventRecord(ctx->prof_ev[ctx->prof_n], s);
+    return true;
+}
+static void prof_end(b200spmv_ctx *ctx, cudaStream_t s)
+{
+    cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s);
+    ctx->prof_n += 2;
+}
+
 template <int DT>
 static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
 {
     const DeviceCsr &m = ctx->csr;
-    const bool strict = flags & B200SPMV_STRICT_ORDER;
+    const bool strict = (flags & B200SPMV_STRICT_ORDER) || !ctx->flagged;
     const bool persist = !(flags & B200SPMV_NO_PERSIST);
     const bool accumulate = flags & B200SPMV_ACCUMULATE;
     const uint64_t *x = (const uint64_t *)ctx->d_x;
@@ -1198,174 +781,107 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
             }
         }
         if (ctx->wait_slab_events) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_slab[sl], 0));
-        if (!strict && ctx->opt_kernel >= 3 && ctx->flagged) {
-            const uint32_t tb = ctx->h_ftile_base[sl];
-            const uint32_t nt = ctx->h_ftile_base[sl + 1] - tb;
-            const bool has_empty = ctx->h_nseg[sl] < rows;
-            if (!read_y && has_empty) B2_CHECK(ctx, cudaMemsetAsync(y, 0, (size_t)rows * 8, s));  // rows no flag will touch
-            const uint32_t *ci = m.colind + ctx->h_slab_off[sl];
-            const uint64_t *va = vals + ctx->h_slab_off[sl];
-            const uint32_t *segrow = m.seg_row + sl * stride, *tseg = m.tile_seg + tb + sl;
-            uint32_t *crow = m.carry_row + tb;
-            uint64_t *cval = (uint64_t *)m.carry_val + tb;
-            const bool prof = ctx->opt_profile && ctx->prof_n + 2 <= 128;
-            if (prof) {
-                if (!ctx->prof_ev[ctx->prof_n]) { cudaEventCreate(&ctx->prof_ev[ctx->prof_n]); cudaEventCreate(&ctx->prof_ev[ctx->prof_n + 1]); }
-                cudaEventRecord(ctx->prof_ev[ctx->prof_n], s);
-            }
-            // hypersparse slab (fewer than opt_dcsr_x16/16 entries per non-empty row and no long row: on a skewed
-            // matrix one thread with a few thousand entries holds the whole launch up): thread per non-empty row
-            const uint32_t nseg = ctx->h_nseg[sl];
-            if (dcsr_slab(ctx, sl)) {
-                const unsigned grid = b2_div_up(nseg, 256);
-                if (persist) {
-                    if (read_y) spmv_dcsr_kernel<DT, true, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
-                    else spmv_dcsr_kernel<DT, true, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
-                } else {
-                    if (read_y) spmv_dcsr_kernel<DT, false, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
-                    else spmv_dcsr_kernel<DT, false, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
-                }
-                if (prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
-                ctx->launches += 1;
-                B2_CHECK(ctx, cudaGetLastError());
-                continue;
-            }
-#define B2_LAUNCH_FLAG(P, R, E)                                                                                     \
-    do {                                                                                                           \
-        if (ctx->opt_ept == 16)                                                                                    \
-            spmv_flag_kernel<DT, P, R, E, 16><<<pn, B2_FLAG_TILE / 16, 0, s>>>(pci, pva, x, y, segrow, rows, ptseg, pcrow, pcval, (uint32_t)ctx->opt_prefetch_tiles); \
-        else                                                                                                       \
-            spmv_flag_kernel<DT, P, R, E, 8><<<pn, B2_FLAG_TILE / 8, 0, s>>>(pci, pva, x, y, segrow, rows, ptseg, pcrow, pcval, (uint32_t)ctx->opt_prefetch_tiles);  \
-    } while (0)
-#define B2_LAUNCH_RING(P, R, E)                                                                                     \
-    do {                                                                                                           \
-        auto kfn = spmv_flag_ring_kernel<DT, P, R, E>;                                                             \
-        static bool attr_set = false;                                                                              \
-        if (!attr_set) {                                                                                           \
-            B2_CHECK(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PK_SMEM_BYTES)); \
-            B2_CHECK(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));         \
-            attr_set = true;                                                                                       \
-        }                                                                                                          \
-        const uint32_t grid = std::min<uint32_t>(nt, (uint32_t)ctx->sms * (uint32_t)ctx->opt_ctas_per_sm);         \
-        kfn<<<grid, B2_FLAG_TILE / 8, PK_SMEM_BYTES, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval, nt);       \
-    } while (0)
-#define B2_LAUNCH_WARP(P, R, E)                                                                                     \
-    do {                                                                                                           \
-        if (ctx->opt_ablate == 1)                                                                                  \
-            spmv_flag_warp_kernel<DT, P, R, E, 1><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
-        else if (ctx->opt_ablate == 2)                                                                             \
-            spmv_flag_warp_kernel<DT, P, R, E, 2><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
-        else if (ctx->opt_ablate == 3)                                                                             \
-            spmv_flag_warp_kernel<DT, P, R, E, 3><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
-        else                                                                                                       \
-            spmv_flag_warp_kernel<DT, P, R, E, 0><<<b2_div_up(nw, 8), 256, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nw); \
-    } while (0)
-            const uint32_t nw = nt * WK_PER_TILE;
-            const uint32_t *wseg = m.warp_seg + (size_t)tb * WK_PER_TILE + sl;
-            uint32_t *wcrow = m.carry_row + (size_t)tb * WK_PER_TILE;
-            uint64_t *wcval = (uint64_t *)m.carry_val + (size_t)tb * WK_PER_TILE;
-            if (ctx->opt_kernel == 5) {
-                if (persist) {
-                    if (read_y) { if (has_empty) B2_LAUNCH_WARP(true, true, true); else B2_LAUNCH_WARP(true, true, false); }
-                    else { if (has_empty) B2_LAUNCH_WARP(true, false, true); else B2_LAUNCH_WARP(true, false, false); }
-                } else {
-                    if (read_y) { if (has_empty) B2_LAUNCH_WARP(false, true, true); else B2_LAUNCH_WARP(false, true, false); }
-                    else { if (has_empty) B2_LAUNCH_WARP(false, false, true); else B2_LAUNCH_WARP(false, false, false); }
-                }
-            } else if (ctx->opt_kernel == 4) {
-                if (persist) {
-                    if (read_y) { if (has_empty) B2_LAUNCH_RING(true, true, true); else B2_LAUNCH_RING(true, true, false); }
-                    else { if (has_empty) B2_LAUNCH_RING(true, false, true); else B2_LAUNCH_RING(true, false, false); }
-                } else {
-                    if (read_y) { if (has_empty) B2_LAUNCH_RING(false, true, true); else B2_LAUNCH_RING(false, true, false); }
-                    else { if (has_empty) B2_LAUNCH_RING(false, false, true); else B2_LAUNCH_RING(false, false, false); }
-                }
-            } else {
-                // kernel 3.  For b200spmv_exec the last slab goes out in Y_CHUNKS pieces of consecutive tiles, each
-                // followed by its own fix-up and an event: the rows a piece completes can leave for the host while
-                // the pieces after it still run (common.cuh, h_chunk_row).
-                const bool chunked = ctx->want_row_chunks && pos == ctx->slabs - 1 && b2_last_slab_chunkable(ctx, flags);
-                const int pieces = chunked ? Y_CHUNKS : 1;
-                for (int k = 0; k < pieces; k++) {
-                    const uint32_t t0 = chunked ? ctx->h_chunk_tile[k] : 0, t1 = chunked ? ctx->h_chunk_tile[k + 1] : nt;
-                    const uint32_t pn = t1 - t0;
-                    if (pn > 0) {
-                        const uint32_t *pci = ci + (size_t)t0 * B2_FLAG_TILE, *ptseg = tseg + t0;
-                        const uint64_t *pva = va + (size_t)t0 * B2_FLAG_TILE;
-                        uint32_t *pcrow = crow + t0;
-                        uint64_t *pcval = cval + t0;
-                        if (persist) {
-                            if (read_y) { if (has_empty) B2_LAUNCH_FLAG(true, true, true); else B2_LAUNCH_FLAG(true, true, false); }
-                            else { if (has_empty) B2_LAUNCH_FLAG(true, false, true); else B2_LAUNCH_FLAG(true, false, false); }
-                        } else {
-                            if (read_y) { if (has_empty) B2_LAUNCH_FLAG(false, true, true); else B2_LAUNCH_FLAG(false, true, false); }
-                            else { if (has_empty) B2_LAUNCH_FLAG(false, false, true); else B2_LAUNCH_FLAG(false, false, false); }
-                        }
-                        ctx->launches += 1;
-                    }
-                    if (k == pieces - 1 && prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
-                    if (!chunked) {
-                        spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
-                        ctx->launches += 1;
-                    } else {
-                        // carries whose run ends before the last tile this piece has run (the last piece: all that is left)
-                        const uint32_t lo = k == 0 ? 0 : std::max(t0, 1u) - 1, hi = k == pieces - 1 ? nt : std::max(t1, 1u) - 1;
-                        if (hi > lo) {
-                            spmv_fixup_range_kernel<DT><<<b2_div_up(hi - lo, 256), 256, 0, s>>>(crow, cval, lo, hi, nt, y);
-                            ctx->launches += 1;
-                        }
-                        B2_CHECK(ctx, cudaEventRecord(ctx->ev_rowchunk[k], s));
-                    }
-                }
-                ctx->did_row_chunks = ctx->did_row_chunks || chunked;
-            }
-#undef B2_LAUNCH_FLAG
-#undef B2_LAUNCH_RING
-#undef B2_LAUNCH_WARP
-            if (ctx->opt_kernel == 5 || ctx->opt_kernel == 4) {
-                if (prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
-                if (ctx->opt_kernel == 5) spmv_fixup_kernel<DT><<<b2_div_up(nw, 256), 256, 0, s>>>(wcrow, wcval, nw, y);
-                else spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
-                ctx->launches += 2;
-            }
-        } else if (strict) {
+        if (strict) {
             const unsigned grid = b2_div_up(rows, 256);
             if (read_y) spmv_rowseq_kernel<DT, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows, ctx->colmask);
             else spmv_rowseq_kernel<DT, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows, ctx->colmask);
             ctx->launches += 1;
-        } else {
-            const uint32_t tb = ctx->h_tile_base[sl];
-            const uint32_t nt = ctx->h_tile_base[sl + 1] - tb;
-            if (nt == 0) continue;
-            const uint32_t *trow = m.tile_row + tb + sl, *tnz = m.tile_nz + tb + sl;
-            uint32_t *crow = m.carry_row + tb;
-            uint64_t *cval = (uint64_t *)m.carry_val + tb;
-#define B2_LAUNCH_MERGE(P, R)                                                                                      \
-    do {                                                                                                           \
-        if (ctx->opt_kernel == 1)                                                                                  \
-            spmv_merge_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval, ctx->colmask); \
-        else                                                                                                       \
-            spmv_merge_tma_kernel<DT, P, R><<<nt, MP_THREADS, 0, s>>>(rowptr, m.colind, vals, x, y, rows, trow, tnz, crow, cval, ctx->colmask); \
-    } while (0)
-            const bool prof = ctx->opt_profile && ctx->prof_n + 2 <= 128;
-            if (prof) {
-                if (!ctx->prof_ev[ctx->prof_n]) { cudaEventCreate(&ctx->prof_ev[ctx->prof_n]); cudaEventCreate(&ctx->prof_ev[ctx->prof_n + 1]); }
-                cudaEventRecord(ctx->prof_ev[ctx->prof_n], s);
-            }
-            if (persist) { if (read_y) B2_LAUNCH_MERGE(true, true); else B2_LAUNCH_MERGE(true, false); }
-            else { if (read_y) B2_LAUNCH_MERGE(false, true); else B2_LAUNCH_MERGE(false, false); }
-#undef B2_LAUNCH_MERGE
-            if (prof) { cudaEventRecord(ctx->prof_ev[ctx->prof_n + 1], s); ctx->prof_n += 2; }
-            spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
-            ctx->launches += 2;
+            B2_CHECK(ctx, cudaGetLastError());
+            continue;
         }
+        const uint32_t tb = ctx->h_ftile_base[sl];
+        const uint32_t nt = ctx->h_ftile_base[sl + 1] - tb;
+        const bool has_empty = ctx->h_nseg[sl] < rows;
+        if (!read_y && has_empty) B2_CHECK(ctx, cudaMemsetAsync(y, 0, (size_t)rows * 8, s));  // rows no flag will touch
+        const uint32_t *ci = m.colind + ctx->h_slab_off[sl];
+        const uint64_t *va = vals + ctx->h_slab_off[sl];
+        const uint32_t *segrow = m.seg_row + sl * stride, *tseg = m.tile_seg + tb + sl;
+        const bool prof = prof_begin(ctx, s);
+        // hypersparse slab (fewer than opt_dcsr_x16/16 entries per non-empty row and no long row: on a skewed
+        // matrix one thread with a few thousand entries holds the whole launch up): thread per non-empty row
+        const uint32_t nseg = ctx->h_nseg[sl];
+        if (dcsr_slab(ctx, sl)) {
+            const unsigned grid = b2_div_up(nseg, 256);
+            if (persist) {
+                if (read_y) spmv_dcsr_kernel<DT, true, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+                else spmv_dcsr_kernel<DT, true, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+            } else {
+                if (read_y) spmv_dcsr_kernel<DT, false, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+                else spmv_dcsr_kernel<DT, false, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+            }
+            if (prof) prof_end(ctx, s);
+            ctx->launches += 1;
+            B2_CHECK(ctx, cudaGetLastError());
+            continue;
+        }
+        // For b200spmv_exec the last slab goes out in Y_CHUNKS pieces of consecutive tiles (kernel 3), each followed
+        // by its own fix-up and an event: the rows a piece completes can leave for the host while the pieces after it
+        // still run (common.cuh, h_chunk_row).
+        const bool chunked = ctx->want_row_chunks && pos == ctx->slabs - 1 && b2_last_slab_chunkable(ctx, flags);
+        if (ctx->opt_kernel == 6 && !chunked) {
+            const uint32_t nwt = nt * WK_PER_TILE;
+            const uint32_t *wseg = m.warp_seg + (size_t)tb * WK_PER_TILE + sl;
+            uint32_t *wcrow = m.carry_row + (size_t)tb * WK_PER_TILE;
+            uint64_t *wcval = (uint64_t *)m.carry_val + (size_t)tb * WK_PER_TILE;
+            const bool db = ctx->opt_stream_db != 0;
+            const uint32_t occ = ctx->opt_stream_occ > 0 ? (uint32_t)ctx->opt_stream_occ : (db ? 2u : 3u);
+            const uint32_t warps = (uint32_t)ctx->sms * occ * (SK_THREADS / 32);
+            const uint32_t chunk = std::max<uint32_t>(1u, b2_div_up(nwt, (uint64_t)warps * (uint32_t)std::max(1, ctx->opt_stream_vchunks)));
+            const uint32_t nchunks = b2_div_up(nwt, chunk);
+            const uint32_t grid = std::min<uint32_t>((uint32_t)ctx->sms * occ, b2_div_up(nchunks, SK_THREADS / 32));
+            const uint32_t pf = (uint32_t)ctx->opt_stream_pf;
+#define B2_CALL_STREAM(P, R, E)                                                                                            \
+    do {                                                                                                                   \
+        if (db) spmv_stream_kernel<DT, P, R, E, true><<<grid, SK_THREADS, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nwt, chunk, nchunks, pf); \
+        else spmv_stream_kernel<DT, P, R, E, false><<<grid, SK_THREADS, 0, s>>>(ci, va, x, y, segrow, rows, wseg, wcrow, wcval, nwt, chunk, nchunks, pf);  \
+    } while (0)
+            B2_DISPATCH3(persist, read_y, has_empty, B2_CALL_STREAM);
+#undef B2_CALL_STREAM
+            if (prof) prof_end(ctx, s);
+            spmv_fixup_kernel<DT><<<b2_div_up(nchunks, 256), 256, 0, s>>>(wcrow, wcval, nchunks, y);
+            ctx->launches += 2;
+            B2_CHECK(ctx, cudaGetLastError());
+            continue;
+        }
+        uint32_t *crow = m.carry_row + tb;
+        uint64_t *cval = (uint64_t *)m.carry_val + tb;
+        const int pieces = chunked ? Y_CHUNKS : 1;
+        for (int k = 0; k < pieces; k++) {
+            const uint32_t t0 = chunked ? ctx->h_chunk_tile[k] : 0, t1 = chunked ? ctx->h_chunk_tile[k + 1] : nt;
+            const uint32_t pn = t1 - t0;
+            if (pn > 0) {
+                const uint32_t *pci = ci + (size_t)t0 * B2_FLAG_TILE, *ptseg = tseg + t0;
+                const uint64_t *pva = va + (size_t)t0 * B2_FLAG_TILE;
+                uint32_t *pcrow = crow + t0;
+                uint64_t *pcval = cval + t0;
+#define B2_CALL_FLAG(P, R, E) \
+    spmv_flag_kernel<DT, P, R, E, 8><<<pn, B2_FLAG_TILE / 8, 0, s>>>(pci, pva, x, y, segrow, rows, ptseg, pcrow, pcval, (uint32_t)ctx->opt_prefetch_tiles)
+                B2_DISPATCH3(persist, read_y, has_empty, B2_CALL_FLAG);
+#undef B2_CALL_FLAG
+                ctx->launches += 1;
+            }
+            if (k == pieces - 1 && prof) prof_end(ctx, s);
+            if (!chunked) {
+                spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
+                ctx->launches += 1;
+            } else {
+                // carries whose run ends before the last tile this piece has run (the last piece: all that is left)
+                const uint32_t lo = k == 0 ? 0 : std::max(t0, 1u) - 1, hi = k == pieces - 1 ? nt : std::max(t1, 1u) - 1;
+                if (hi > lo) {
+                    spmv_fixup_range_kernel<DT><<<b2_div_up(hi - lo, 256), 256, 0, s>>>(crow, cval, lo, hi, nt, y);
+                    ctx->launches += 1;
+                }
+                B2_CHECK(ctx, cudaEventRecord(ctx->ev_rowchunk[k], s));
+            }
+        }
+        ctx->did_row_chunks = ctx->did_row_chunks || chunked;
         B2_CHECK(ctx, cudaGetLastError());
     }
-    ctx->last_mode = strict ? 0 : ((ctx->opt_kernel >= 3 && !ctx->flagged) ? 2 : ctx->opt_kernel);
+    ctx->last_mode = strict ? 0 : ctx->opt_kernel;
     return 0;
 }
 
-// Fold the recorded merge-kernel event pairs into merge_kernel_ns (call after a sync).
+// Fold the recorded kernel event pairs into merge_kernel_ns (call after a sync).
 void b2_profile_collect(b200spmv_ctx *ctx)
 {
     for (int i = 0; i + 1 < ctx->prof_n; i += 2) {
@@ -1389,22 +905,6 @@ int b2_spmv_prepare(b200spmv_ctx *ctx, int flags, cudaStream_t s)
     if (persist != ctx->persist_set) {
         B2_TRY(set_persist_window(ctx, s, ctx->d_x, (size_t)ctx->cols * 8, persist));
         ctx->persist_set = persist;
-    }
-    static bool carveout_set = false;
-    if (!carveout_set) {
-#define B2_CARVE(DT) \
-    cudaFuncSetAttribute(spmv_merge_kernel<DT, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
-    cudaFuncSetAttribute(spmv_merge_kernel<DT, true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
-    cudaFuncSetAttribute(spmv_merge_kernel<DT, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
-    cudaFuncSetAttribute(spmv_merge_kernel<DT, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
-    cudaFuncSetAttribute(spmv_merge_tma_kernel<DT, true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
-    cudaFuncSetAttribute(spmv_merge_tma_kernel<DT, true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
-    cudaFuncSetAttribute(spmv_merge_tma_kernel<DT, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100); \
-    cudaFuncSetAttribute(spmv_merge_tma_kernel<DT, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-        B2_CARVE(B200SPMV_F64)
-        B2_CARVE(B200SPMV_U64)
-#undef B2_CARVE
-        carveout_set = true;
     }
     return 0;
 }

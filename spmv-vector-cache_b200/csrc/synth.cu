@@ -111,6 +111,10 @@ int b2_synth_build_csc(b200spmv_ctx *ctx, int kind, uint32_t npr, uint64_t seed)
     } else if (kind == SYNTH_BANDED) {
         if (rows != cols || rows < 2 * SYNTH_BAND_HALF + 1) return b2_fail(ctx, B200SPMV_EINVAL, "banded matrix must be square, n >= 11");
         expect += (uint64_t)rows * (2 * SYNTH_BAND_HALF + 1) - SYNTH_BAND_HALF * (SYNTH_BAND_HALF + 1);
+    } else if (kind == SYNTH_BAND) {
+        if (rows != cols || rows < npr) return b2_fail(ctx, B200SPMV_EINVAL, "pure band matrix must be square, n >= nnz_per_row");
+        const uint64_t h = npr / 2, u = npr - 1 - h;  // rows clipped at the top lose h, h-1, ...; at the bottom u, u-1, ...
+        expect -= h * (h + 1) / 2 + u * (u + 1) / 2;
     } else if (kind != SYNTH_UNIFORM) {
         return b2_fail(ctx, B200SPMV_EINVAL, "unknown synthetic kind");
     }

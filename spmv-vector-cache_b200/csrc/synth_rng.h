@@ -25,6 +25,7 @@
 #define SYNTH_UNIFORM 0 /* nnz_per_row uniform-random columns per row, sorted, dups kept */
 #define SYNTH_RMAT 1    /* Graph500 R-MAT (0.57,0.19,0.19,0.05), edge factor = nnz_per_row */
 #define SYNTH_BANDED 2  /* 11-wide band (offsets -5..+5, clipped) + nnz_per_row random cols */
+#define SYNTH_BAND 3    /* pure band: nnz_per_row consecutive columns from r - nnz_per_row/2, clipped */
 
 #define SYNTH_BAND_HALF 5
 
@@ -116,9 +117,22 @@ SYNTH_HD uint32_t synth_band_count(uint32_t r, uint32_t n)
 
 #define SYNTH_MAX_NPR 64
 
+// pure band (SYNTH_BAND): row r holds columns [lo, hi] = [r - npr/2, r - npr/2 + npr - 1] clipped to the matrix
+SYNTH_HD void synth_pure_band_range(uint32_t r, uint32_t cols, uint32_t npr, uint32_t *lo, uint32_t *hi)
+{
+    const int64_t first = (int64_t)r - (int64_t)(npr / 2), last = first + (int64_t)npr - 1;
+    *lo = first < 0 ? 0u : (uint32_t)first;
+    *hi = last >= (int64_t)cols ? cols - 1 : (uint32_t)last;
+}
+
 // length of row r for the row-generated kinds
 SYNTH_HD uint32_t synth_row_len(int kind, uint32_t r, uint32_t rows, uint32_t npr)
 {
+    if (kind == SYNTH_BAND) {
+        uint32_t lo, hi;
+        synth_pure_band_range(r, rows, npr, &lo, &hi);
+        return hi - lo + 1;
+    }
     return kind == SYNTH_BANDED ? synth_band_count(r, rows) + npr : npr;
 }
 
@@ -128,6 +142,15 @@ SYNTH_HD uint32_t synth_row_len(int kind, uint32_t r, uint32_t rows, uint32_t np
 SYNTH_HD uint32_t synth_gen_row(int kind, uint64_t seed, uint32_t r, uint32_t rows, uint32_t cols,
                                 uint32_t npr, int dtype_u64, uint32_t *out_col, uint64_t *out_val)
 {
+    if (kind == SYNTH_BAND) {
+        uint32_t lo, hi;
+        synth_pure_band_range(r, cols, npr, &lo, &hi);
+        for (uint32_t c = lo; c <= hi; c++) {
+            out_col[c - lo] = c;
+            out_val[c - lo] = synth_value_bits(seed, r, c - lo, dtype_u64, kind, 0);
+        }
+        return hi - lo + 1;
+    }
     uint32_t draws[SYNTH_MAX_NPR];
     for (uint32_t k = 0; k < npr; k++) {
         uint32_t c = synth_below(synth_hash(seed, r, k), cols);

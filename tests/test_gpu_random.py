@@ -52,7 +52,7 @@ def test_random_matrices_every_kernel(oracle, case, dtype):
     if dtype == "f64":
         oracle.lib.oracle_row_abs_sums_f64(H.C.c_uint32(rows), H.C.c_uint32(cols), H.ptr(colptr), H.ptr(rowind),
                                            H.ptr(vals), H.ptr(x), H.ptr(abs_sum), H.ptr(row_nnz))
-    for kernel, dcsr, slabs in ((3, 0, 1), (3, 0, 3), (5, 0, 2), (4, 0, 1), (2, 0, 2), (1, 0, 1), (3, 1 << 20, 2), (3, 96, 4)):
+    for kernel, dcsr, slabs in ((3, 0, 1), (3, 0, 3), (6, 0, 1), (6, 0, 2), (6, 0, 5), (6, 1 << 20, 2), (6, 96, 4)):
         e = b2.Engine(0)
         e.set_option("kernel", kernel)
         e.set_option("dcsr_x16", dcsr)

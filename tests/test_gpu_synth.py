@@ -20,7 +20,7 @@ def DT(b2, dtype):
     return b2.F64 if dtype == "f64" else b2.U64
 
 
-@pytest.mark.parametrize("kind,rows,npr", [(0, 5000, 32), (0, 777, 1), (2, 4099, 5), (1, 4096, 8), (1, 1 << 14, 32)])
+@pytest.mark.parametrize("kind,rows,npr", [(0, 5000, 32), (0, 777, 1), (2, 4099, 5), (1, 4096, 8), (1, 1 << 14, 32), (3, 3000, 16), (3, 129, 7)])
 @pytest.mark.parametrize("dtype", ["f64", "u64"])
 @pytest.mark.parametrize("slabs", [1, 3])
 def test_synthetic_small_vs_oracle(b2, oracle, kind, rows, npr, dtype, slabs):

@@ -26,7 +26,7 @@ def check(name, ok):
 cases = [(0, 1 << 17, 8, 2, {}), (1, 1 << 17, 8, 3, {}), (2, (1 << 17) + 777, 5, 2, {"dcsr_x16": 0}),
          (0, 1 << 17, 4, 1, {"pin_host": 1}),
          (0, 5000, 3, 4, {"prefetch_x": 1}), (1, 4096, 16, 2, {"dcsr_maxrow": 1 << 30, "dcsr_x16": 1 << 20}),
-         (2, 4099, 5, 3, {"world": 3, "rank": 1, "own_slabs": 1}), (0, 3000, 32, 1, {"kernel": 5}), (0, 3000, 32, 2, {"kernel": 1})]
+         (2, 4099, 5, 3, {"world": 3, "rank": 1, "own_slabs": 1}), (0, 3000, 32, 1, {"kernel": 3}), (0, 3000, 32, 2, {"kernel": 6, "stream_db": 0, "stream_pf": 2})]
 for kind, rows, npr, slabs, opts in cases:
     for dtype in (b2.U64, b2.F64):
         e = b2.Engine(0)
