@@ -30,16 +30,21 @@ ORACLE_API uint64_t synth_host_nnz(int kind, uint32_t rows, uint32_t npr)
     return (uint64_t)rows * npr;
 }
 
-/* CSR of the row-generated kinds (UNIFORM, BANDED, BAND). */
+/* CSR of the row-generated kinds (UNIFORM, BANDED, BAND).  Rows are independent pure functions of (seed, r),
+ * so the row loop is an OpenMP parallel-for when the library is built with -fopenmp (bench.py materialises the
+ * 16M x 16M x 32 headline matrix on the host for the reference arm). */
 ORACLE_API void synth_host_csr(int kind, uint64_t seed, uint32_t rows, uint32_t cols, uint32_t npr,
                                int dtype_u64, uint32_t *rowptr, uint32_t *colind, uint64_t *vals)
 {
     uint32_t p = 0;
     for (uint32_t r = 0; r < rows; r++) {
         rowptr[r] = p;
-        p += synth_gen_row(kind, seed, r, rows, cols, npr, dtype_u64, colind + p, vals + p);
+        p += synth_row_len(kind, r, rows, npr);
     }
     rowptr[rows] = p;
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < (int64_t)rows; r++)
+        synth_gen_row(kind, seed, (uint32_t)r, rows, cols, npr, dtype_u64, colind + rowptr[r], vals + rowptr[r]);
 }
 
 /* COO edge list of the R-MAT kind, in edge order (rows = cols = 1 << scale). */

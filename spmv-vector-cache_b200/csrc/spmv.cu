@@ -5,8 +5,8 @@
 //       contiguous chunk of the slab's entry stream and walks it 256 entries at a time; the two 12 B/entry
 //       streams of the NEXT step are already in flight (register double buffer, optional L2 bulk prefetch)
 //       while the x gathers and the row logic of the current one run, the open row travels in a register
-//       from step to step, and only one carry per chunk is left for spmv_fixup_kernel.  No shared memory,
-//       no block barrier, no row pointers.
+//       from step to step, and only one carry per chunk is left for spmv_fixup_kernel.  No block barrier,
+//       no row pointers; y is read and written with coalesced requests.
 //   spmv_flag_kernel (3) : the same flagged arithmetic with one 2048-entry tile per (non-persistent) CTA.
 //       Kept because its tiles are consecutive pieces of the rows: b200spmv_exec launches the last slab in
 //       pieces of tiles and sends finished rows to the host while later pieces run.
@@ -246,28 +246,16 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
 //     HBM reads in flight.  A non-persistent CTA spends most of its life NOT loading streams (launch, gather
 //     round trip, row logic, y round trip, exit), which is what held kernel 3 near 200 GNNZ/s whatever the
 //     gather locality;
-//   * no shared memory and no block barrier: the warps of an SM are independent chains;
-//   * accumulating launches (y += ..., and every slab after the first) add their row sums with a reduction
-//     at L2 (red.global.add) instead of load / add / store: one request instead of two and no y round trip.
+//   * no block barrier: the warps of an SM are independent chains;
+//   * the sums of the rows a step closes go through a warp-private strip of shared memory to the lanes that
+//     write them out, so y is read and written with coalesced requests (see stream_step).
 constexpr int SK_THREADS = 256;
 constexpr int WK_ENTRIES = 256;  // per warp step: 32 lanes x 8 entries
 constexpr int WK_PER_TILE = (int)(B2_FLAG_TILE / WK_ENTRIES);
 
 #ifndef B200SPMV_ABLATE
-#define B200SPMV_ABLATE 0  // measurement builds only (make ablate): 1 no y stores, 2 no scan, 3 no row logic, 4 no gathers
+#define B200SPMV_ABLATE 0  // measurement builds only (make ablate): 1 no y stores, 3 no row logic, 4 no gathers either
 #endif
-
-// y[row] (+)= v.  Each row is closed by exactly one thread of a launch, so the reduction meets no contention and
-// gives the same single rounded addition y_old + v a load / add / store would.
-template <int DT, bool READ_Y>
-__device__ __forceinline__ void emit_row(uint64_t *__restrict__ y, uint32_t row, uint64_t v)
-{
-    if (!READ_Y) { y[row] = v; return; }
-    if (DT == B200SPMV_F64)
-        asm volatile("red.global.add.f64 [%0], %1;" ::"l"(y + row), "d"(__longlong_as_double((long long)v)) : "memory");
-    else
-        asm volatile("red.global.add.u64 [%0], %1;" ::"l"(y + row), "l"(v) : "memory");
-}
 
 __device__ __forceinline__ void stream_load(uint32_t (&c)[8], uint64_t (&p)[8], const uint32_t *cp, const uint64_t *vp)
 {
@@ -279,16 +267,25 @@ __device__ __forceinline__ void stream_load(uint32_t (&c)[8], uint64_t (&p)[8], 
 // One warp step: 256 consecutive entries, c / p = this lane's 8 column ids (flag in bit 31) and values.
 // segs_base = row-start flags before the step's first entry, wcarry = partial sum of the row open on entry;
 // both are advanced to the end of the step.
+//
+// Every flag closes the row before it.  The sums of the rows a step closes are collected in a warp-private
+// shared-memory strip sv[] -- slot j = j-th row closed by the step, i.e. segment segs_base - 1 + j -- and written
+// out by lane j: consecutive segments are (nearly) consecutive rows, so y is read and written with ONE coalesced
+// load and ONE coalesced store per 32 closed rows.  (Round-2 measurement: letting every closing thread update y
+// itself, by load/add/store or by red.global.add, costs an L2 request per row; on a gather-bound matrix the
+// SM's L2 request port is the bottleneck, and those requests took 8 % (uniform) to 17 % (band) of the step.)
+// The row ids and the old y of the first 32 closed rows are requested before the gathers go out.
 template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY>
 __device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p)[8], const uint64_t *__restrict__ x,
                                             uint64_t *__restrict__ y, const uint32_t *__restrict__ seg_row, uint32_t rows,
-                                            int lane, uint32_t lt, uint64_t pol_keep, uint32_t &segs_base, uint64_t &wcarry)
+                                            int lane, uint32_t lt, uint64_t pol_keep, uint64_t *__restrict__ sv,
+                                            uint32_t &segs_base, uint64_t &wcarry)
 {
     constexpr int ABL = B200SPMV_ABLATE;
     uint64_t xv[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) xv[i] = ABL >= 4 ? (uint64_t)c[i] : load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
     if (ABL >= 3) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) xv[i] = ABL >= 4 ? (uint64_t)c[i] : load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
         uint64_t a = 0;
 #pragma unroll
         for (int i = 0; i < 8; i++) a = Semi<DT>::add(a, Semi<DT>::mul(p[i], xv[i]));
@@ -308,21 +305,32 @@ __device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p
         warp_flags += __popc(bal_b) << bit;
     }
     const uint32_t bal = __ballot_sync(0xffffffffu, nfl != 0);
-    const uint32_t segs_before = segs_base + lane_prefix;
-    // the row my first flag closes (its id is looked up while the gathers are in flight)
-    uint32_t close_row = NO_ROW;
-    if (nfl != 0 && segs_before != 0) {
-        close_row = HAS_EMPTY ? __ldg(seg_row + segs_before - 1) : segs_before - 1;
-        if (close_row >= rows) close_row = NO_ROW;
+    // write-out duty of this lane: the lane-th row the step closes (slot 0 of the very first step of a slab closes
+    // nothing: no row precedes the first flag)
+    const uint32_t my_seg = segs_base + (uint32_t)lane - 1u;
+    uint32_t my_row = NO_ROW;
+    if ((uint32_t)lane < warp_flags && my_seg != 0xFFFFFFFFu) {
+        my_row = HAS_EMPTY ? __ldg(seg_row + my_seg) : my_seg;
+        if (my_row >= rows) my_row = NO_ROW;
     }
-    // branch-free sequential pass: head = sum before my first flag, acc = sum after my last flag
+#pragma unroll
+    for (int i = 0; i < 8; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
+    uint64_t y_old = 0;
+    if (READ_Y && my_row != NO_ROW) y_old = y[my_row];
+
+    // branch-free sequential pass: head = sum before my first flag, acc = sum after my last flag; the rows that
+    // begin and end inside my 8 entries go straight to their slots
     const uint32_t f1 = f & (0u - f);
+    uint64_t *slot = sv + lane_prefix;  // slot of the row my next flag closes
     uint64_t acc = 0, head = 0;
 #pragma unroll
     for (int i = 0; i < 8; i++) {
         p[i] = Semi<DT>::mul(p[i], xv[i]);
-        head = ((f1 >> i) & 1u) ? acc : head;
-        acc = ((f >> i) & 1u) ? 0ull : acc;
+        const bool fl = (f >> i) & 1u, first = (f1 >> i) & 1u;
+        head = first ? acc : head;
+        if (fl && !first) *slot = acc;
+        slot += fl;
+        acc = fl ? 0ull : acc;
         acc = Semi<DT>::add(acc, p[i]);
     }
     // segmented inclusive scan of the open tails over the warp: S = sum of tails from the nearest flagged lane at
@@ -330,50 +338,35 @@ __device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p
     const uint32_t below = bal & ((2u << lane) - 1u);
     const int start = below ? 31 - __clz(below) : 0;
     uint64_t S = acc;
-    if (ABL < 2) {
-        const int span = __reduce_max_sync(0xffffffffu, lane - start);
+    const int span = __reduce_max_sync(0xffffffffu, lane - start);
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            if (d > span) break;
-            const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
-            if (lane - d >= start) S = Semi<DT>::add(n, S);
-        }
+    for (int d = 1; d < 32; d <<= 1) {
+        if (d > span) break;
+        const uint64_t n = __shfl_up_sync(0xffffffffu, S, d);
+        if (lane - d >= start) S = Semi<DT>::add(n, S);
     }
     uint64_t prev = __shfl_up_sync(0xffffffffu, S, 1);  // open partial that ends at lane - 1
     if (lane == 0) prev = 0;
     const uint64_t s31 = __shfl_sync(0xffffffffu, S, 31);
-    if (ABL >= 1) {
-        uint64_t a = Semi<DT>::add(prev, head) ^ (uint64_t)close_row;
-#pragma unroll
-        for (int i = 0; i < 8; i++) a ^= p[i];
-        wcarry ^= a ^ s31;
-        segs_base += warp_flags;
-        return;
-    }
     if (nfl != 0) {
-        if (close_row != NO_ROW) {
-            // no flagged lane below me: the row was open when the step began, its earlier part is wcarry
-            uint64_t val = (bal & lt) == 0 ? Semi<DT>::add(wcarry, prev) : prev;
-            val = Semi<DT>::add(val, head);
-            emit_row<DT, READ_Y>(y, close_row, val);
-        }
-        if (nfl > 1) {  // rows that begin and end inside my 8 entries
-            uint64_t a = 0;
-            uint32_t k = 0;
-#pragma unroll
-            for (int i = 0; i < 8; i++) {
-                if ((f >> i) & 1u) {
-                    if (k != 0) {
-                        const uint32_t row = HAS_EMPTY ? __ldg(seg_row + segs_before + k - 1) : segs_before + k - 1;
-                        if (row < rows) emit_row<DT, READ_Y>(y, row, a);
-                    }
-                    k++;
-                    a = 0;
-                }
-                a = Semi<DT>::add(a, p[i]);
-            }
+        // my first flag closes the row open before my entries; with no flagged lane below me that row was open
+        // when the step began and its earlier part is wcarry
+        const uint64_t val = (bal & lt) == 0 ? Semi<DT>::add(wcarry, prev) : prev;
+        sv[lane_prefix] = Semi<DT>::add(val, head);
+    }
+    __syncwarp();
+    if (my_row != NO_ROW) {
+        const uint64_t v = READ_Y ? Semi<DT>::add(y_old, sv[lane]) : sv[lane];
+        if (ABL >= 1) wcarry ^= v; else y[my_row] = v;
+    }
+    for (uint32_t j = 32u + (uint32_t)lane; j < warp_flags; j += 32u) {  // short rows: more than 32 closed in one step
+        uint32_t row = HAS_EMPTY ? __ldg(seg_row + segs_base + j - 1u) : segs_base + j - 1u;
+        if (row < rows) {
+            const uint64_t v = READ_Y ? Semi<DT>::add(y[row], sv[j]) : sv[j];
+            if (ABL >= 1) wcarry ^= v; else y[row] = v;
         }
     }
+    __syncwarp();  // sv is rewritten by the next step
     wcarry = bal ? s31 : Semi<DT>::add(wcarry, s31);
     segs_base += warp_flags;
 }
@@ -392,6 +385,8 @@ spmv_stream_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restri
     const uint32_t lt = (1u << lane) - 1u;
     const uint64_t pol_keep = policy_evict_last();
     const uint32_t nwarps = gridDim.x * (SK_THREADS / 32);
+    __shared__ uint64_t s_close[SK_THREADS / 32][WK_ENTRIES];  // per warp: sums of the rows the current step closes
+    uint64_t *sv = s_close[threadIdx.x >> 5];
 #define B2_STREAM_PREFETCH()                                                                                              \
     if (pf_dist != 0 && lane == 0 && t + pf_dist < t1) {                                                                  \
         const uint64_t e = (uint64_t)(t + pf_dist) * WK_ENTRIES;                                                          \
@@ -399,7 +394,7 @@ spmv_stream_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restri
         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(colind + e), "r"(WK_ENTRIES * 4u) : "memory");    \
     }
 #define B2_STREAM_STEP(C, P) \
-    stream_step<DT, PERSIST, READ_Y, HAS_EMPTY>(C, P, x, y, seg_row, rows, lane, lt, pol_keep, segs_base, wcarry)
+    stream_step<DT, PERSIST, READ_Y, HAS_EMPTY>(C, P, x, y, seg_row, rows, lane, lt, pol_keep, sv, segs_base, wcarry)
     for (uint32_t vc = blockIdx.x * (SK_THREADS / 32) + (threadIdx.x >> 5); vc < nchunks; vc += nwarps) {
         uint32_t t = vc * chunk;
         const uint32_t t1 = min(t + chunk, nwt);

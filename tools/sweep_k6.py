@@ -1,9 +1,8 @@
 #!/usr/bin/env python
 """Kernel sweep on one B200 (numpy + ctypes only): for a few workloads, set the matrix up once and time the SpMV
 step (b200spmv_exec_device, CUDA events, y += A*x) under different launch-time options of kernels 3 and 6.
-Every configuration is first checked against the strict kernel in u64?  No: timing only; parity is pytest's job,
-but each timed configuration's y is compared with the first configuration's y (same matrix, same x, fp64
-re-association only) so that a variant that skips work shows up.
+Timing only -- parity is pytest's job -- but each timed configuration's y is compared with the first
+configuration's y (same matrix, same x, fp64 re-association only), so a variant that skips work shows up.
 
   python tools/sweep_k6.py [--quick] [--only NAME] > gpurun_out/sweep.txt
   B200SPMV_LIB=.../build/libb200spmv_abl3.so python tools/sweep_k6.py --ablate   (measurement builds, no check)
@@ -38,8 +37,8 @@ args = ap.parse_args()
 # (name, kind, rows, npr, slabs list)
 WORK = [
     ("uniform C3", 0, 1 << 24, 32, [0]),
-    ("band16", 3, 1 << 24, 16, [1, 0]),
-    ("banded11+5", 2, 1 << 24, 5, [1, 0]),
+    ("band16", 3, 1 << 24, 16, [1, 3]),
+    ("banded11+5", 2, 1 << 24, 5, [1, 3]),
     ("rmat16M", 1, 1 << 24, 32, [0]),
     ("uniform 4M (x in L2)", 0, 1 << 22, 32, [1]),
 ]
@@ -51,17 +50,15 @@ if args.only:
 VARIANTS = [
     ("k3", {"kernel": 3}),
     ("k6 db occ2", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1}),
-    ("k6 db occ2 pf4", {"kernel": 6, "stream_db": 1, "stream_pf": 4, "stream_occ": 0, "stream_vchunks": 1}),
     ("k6 db occ2 v8", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 8}),
     ("k6 nodb occ3", {"kernel": 6, "stream_db": 0, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1}),
-    ("k6 nodb occ3 pf2", {"kernel": 6, "stream_db": 0, "stream_pf": 2, "stream_occ": 0, "stream_vchunks": 1}),
-    ("k6 nodb occ3 pf4", {"kernel": 6, "stream_db": 0, "stream_pf": 4, "stream_occ": 0, "stream_vchunks": 1}),
-    ("k6 nodb occ3 pf4 v8", {"kernel": 6, "stream_db": 0, "stream_pf": 4, "stream_occ": 0, "stream_vchunks": 8}),
-    ("k6 nodb occ2", {"kernel": 6, "stream_db": 0, "stream_pf": 0, "stream_occ": 2, "stream_vchunks": 1}),
-    ("k6 db occ1", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 1, "stream_vchunks": 1}),
+    ("k6 nodb occ3 v8", {"kernel": 6, "stream_db": 0, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 8}),
+    ("k6 nodb occ3 pf1", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1}),
+    ("k6 db occ2 nopersist", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1, "_flags": 4}),
+    ("k6 db occ2 dcsr0", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1, "dcsr_x16": 0}),
 ]
 if args.ablate:
-    VARIANTS = [v for v in VARIANTS if v[0] in ("k6 db occ2", "k6 nodb occ3", "k6 nodb occ3 pf4")]
+    VARIANTS = [v for v in VARIANTS if v[0] in ("k6 db occ2", "k6 nodb occ3", "k6 nodb occ3 v8")]
 
 print("lib %s  peak %.1f GB/s  steps %d (y += A*x, fp64)" % (b2.LIB_PATH, PEAK, args.steps), flush=True)
 for name, kind, rows, npr, slab_list in WORK:
@@ -81,15 +78,18 @@ for name, kind, rows, npr, slab_list in WORK:
             flush=True)
         ref = None
         for vname, opts in VARIANTS:
+            e.set_option("dcsr_x16", 96)
+            fl = b2.ACCUMULATE | opts.get("_flags", 0)
             for k, v in opts.items():
-                e.set_option(k, v)
+                if not k.startswith("_"):
+                    e.set_option(k, v)
             e.fill_y_zero()
-            e.exec_device(3, b2.ACCUMULATE)
+            e.exec_device(3, fl)
             e.fill_y_zero()
-            ms = e.exec_device(args.steps, b2.ACCUMULATE)
+            ms = e.exec_device(args.steps, fl)
             y = None if args.ablate else e.get_y()
             e.set_option("profile", 1)
-            e.exec_device(5, b2.ACCUMULATE)
+            e.exec_device(5, fl)
             kns, kn = e.stat("merge_kernel_ns"), e.stat("merge_kernel_launches")
             per_slab = [e.stat("slab_ns_%d" % i) * 1e-6 / 5 for i in range(ns)]
             e.set_option("profile", 0)
