@@ -266,6 +266,10 @@ extern "C" int b200spmv_setup_csc(b200spmv_ctx *ctx, uint32_t rows, uint32_t col
     B2_CHECK(ctx, cudaMemcpyAsync(d_vals, vals, (size_t)nnz * 8, cudaMemcpyHostToDevice, s));
     B2_CHECK(ctx, cudaStreamSynchronize(s));
     ctx->csc_colptr = d_colptr; ctx->csc_rowind = d_rowind; ctx->csc_vals = d_vals;
+    {   // nothing below may index with unchecked caller data (device atomics and scatters)
+        const int rc = b2_validate_indices(ctx, d_rowind, nnz, index_mask, rows, d_colptr, cols, s);
+        if (rc) { release_matrix(ctx); return rc; }
+    }
     ctx->row_begin = 0; ctx->row_end = rows; ctx->local_rows = rows; ctx->local_nnz = nnz;
     if (ctx->world > 1) B2_TRY(b2_shard_csc(ctx, index_mask));
     B2_TRY(csc_to_csr(ctx, index_mask));

@@ -215,6 +215,8 @@ int b2_compress(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *k
                 const uint32_t *src_other, const void *src_vals, uint32_t *dst_ptr, uint32_t dst_ptr_add,
                 uint32_t *dst_ind, void *dst_vals, cudaStream_t s);
 int b2_add_u32(b200spmv_ctx *ctx, uint32_t *a, uint64_t n, uint32_t add, cudaStream_t s);
+int b2_validate_indices(b200spmv_ctx *ctx, const uint32_t *d_ind, uint64_t n, uint32_t mask, uint32_t limit,
+                        const uint32_t *d_ptr, uint64_t nptr, cudaStream_t s);
 int b2_count_nonempty(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *key, uint32_t key_mask,
                       uint32_t key_sub, uint64_t *out, cudaStream_t s);
 // spmv.cu

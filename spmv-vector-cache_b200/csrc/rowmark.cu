@@ -58,7 +58,7 @@ __global__ void col_span_kernel(const uint32_t *__restrict__ colptr, const uint3
     const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c < cols) {
         const uint32_t b = colptr[c], e = colptr[c + 1];
-        if (e != 0 && b < nnz) best = inds[e - 1] - inds[b];
+        if (e != 0 && e <= nnz && b < nnz) best = inds[e - 1] - inds[b];
     }
     for (int d = 16; d > 0; d >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, d));
     if ((threadIdx.x & 31) == 0) atomicMax(out, best);
@@ -91,6 +91,7 @@ extern "C" int b200spmv_mark_row_starts(b200spmv_ctx *ctx, uint32_t rows, uint32
     B2_TRY(b2_alloc(ctx, &d, nnz));
     int rc = 0;
     if (cudaMemcpyAsync(d, inds, (size_t)nnz * 4, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) rc = b2_fail(ctx, B200SPMV_ECUDA, "H2D failed");
+    if (!rc) rc = b2_validate_indices(ctx, d, nnz, ROW_MASK, rows, nullptr, 0, ctx->stream);
     if (!rc) rc = mark_on_device(ctx, rows, nnz, d, reverse, shift, ctx->stream);
     if (!rc && (cudaMemcpyAsync(inds, d, (size_t)nnz * 4, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)) rc = b2_fail(ctx, B200SPMV_ECUDA, "D2H failed");
     cudaFree(d);
@@ -111,6 +112,7 @@ extern "C" int b200spmv_max_alive(b200spmv_ctx *ctx, uint32_t rows, uint32_t nnz
         if ((rc = b2_alloc(ctx, &delta, nnz))) break;
         if ((rc = b2_alloc(ctx, &d_out, 1))) break;
         if (cudaMemcpyAsync(d, inds, (size_t)nnz * 4, cudaMemcpyHostToDevice, s) != cudaSuccess) { rc = b2_fail(ctx, B200SPMV_ECUDA, "H2D failed"); break; }
+        if ((rc = b2_validate_indices(ctx, d, nnz, ROW_MASK, rows, nullptr, 0, s))) break;
         if ((rc = mark_on_device(ctx, rows, nnz, d, 0, 31, s))) break;
         if ((rc = mark_on_device(ctx, rows, nnz, d, 1, 30, s))) break;
         const unsigned grid = (unsigned)std::min<uint64_t>(b2_div_up(nnz, 256), (uint64_t)ctx->sms * 32);

@@ -253,6 +253,9 @@ constexpr int SK_THREADS = 256;
 constexpr int WK_ENTRIES = 256;  // per warp step: 32 lanes x 8 entries
 constexpr int WK_PER_TILE = (int)(B2_FLAG_TILE / WK_ENTRIES);
 
+#ifndef B200SPMV_YPF
+#define B200SPMV_YPF 1  // 0: no L2 prefetch of y / seg_row ahead of the warp (A/B builds)
+#endif
 #ifndef B200SPMV_ABLATE
 #define B200SPMV_ABLATE 0  // measurement builds only (make ablate): 1 no y stores, 3 no row logic, 4 no gathers either
 #endif
@@ -275,7 +278,7 @@ __device__ __forceinline__ void stream_load(uint32_t (&c)[8], uint64_t (&p)[8], 
 // itself, by load/add/store or by red.global.add, costs an L2 request per row; on a gather-bound matrix the
 // SM's L2 request port is the bottleneck, and those requests took 8 % (uniform) to 17 % (band) of the step.)
 // The row ids and the old y of the first 32 closed rows are requested before the gathers go out.
-template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY>
+template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, bool Y_PF>
 __device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p)[8], const uint64_t *__restrict__ x,
                                             uint64_t *__restrict__ y, const uint32_t *__restrict__ seg_row, uint32_t rows,
                                             int lane, uint32_t lt, uint64_t pol_keep, uint64_t *__restrict__ sv,
@@ -317,6 +320,19 @@ __device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p
     for (int i = 0; i < 8; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
     uint64_t y_old = 0;
     if (READ_Y && my_row != NO_ROW) y_old = y[my_row];
+    // A warp walks its rows in ascending order, warp_flags of them per step.  y (and the row-id table) of the rows
+    // three steps ahead are pulled into L2 now: otherwise each step waits for a DRAM round trip of its y_old (and,
+    // before it, of its seg_row line) that is longer than the whole gather phase (ncu, round 2: long-scoreboard
+    // stalls with the L2 request port only 71 % busy).
+    if (Y_PF) {
+        const uint32_t ahead = segs_base + 3u * warp_flags;  // segment index ~3 steps ahead
+        if (HAS_EMPTY && lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(seg_row + min(ahead, rows)));
+        if (READ_Y) {
+            const uint32_t r0 = __shfl_sync(0xffffffffu, my_row, 0);  // first row this step closes
+            const uint64_t r = (uint64_t)r0 + 3u * warp_flags + 16u * (uint32_t)lane;
+            if (r0 != NO_ROW && 16u * (uint32_t)lane < warp_flags + 16u && r < rows) asm volatile("prefetch.global.L2 [%0];" ::"l"(y + r));
+        }
+    }
 
     // branch-free sequential pass: head = sum before my first flag, acc = sum after my last flag; the rows that
     // begin and end inside my 8 entries go straight to their slots
@@ -383,18 +399,18 @@ spmv_stream_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restri
 {
     const int lane = threadIdx.x & 31;
     const uint32_t lt = (1u << lane) - 1u;
-    const uint64_t pol_keep = policy_evict_last();
+    const uint64_t pol_keep = policy_evict_last(), pol_stream = policy_evict_first();
     const uint32_t nwarps = gridDim.x * (SK_THREADS / 32);
     __shared__ uint64_t s_close[SK_THREADS / 32][WK_ENTRIES];  // per warp: sums of the rows the current step closes
     uint64_t *sv = s_close[threadIdx.x >> 5];
 #define B2_STREAM_PREFETCH()                                                                                              \
     if (pf_dist != 0 && lane == 0 && t + pf_dist < t1) {                                                                  \
         const uint64_t e = (uint64_t)(t + pf_dist) * WK_ENTRIES;                                                          \
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vals + e), "r"(WK_ENTRIES * 8u) : "memory");      \
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(colind + e), "r"(WK_ENTRIES * 4u) : "memory");    \
+        asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" ::"l"(vals + e), "r"(WK_ENTRIES * 8u), "l"(pol_stream) : "memory");   \
+        asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" ::"l"(colind + e), "r"(WK_ENTRIES * 4u), "l"(pol_stream) : "memory"); \
     }
 #define B2_STREAM_STEP(C, P) \
-    stream_step<DT, PERSIST, READ_Y, HAS_EMPTY>(C, P, x, y, seg_row, rows, lane, lt, pol_keep, sv, segs_base, wcarry)
+    stream_step<DT, PERSIST, READ_Y, HAS_EMPTY, B200SPMV_YPF != 0>(C, P, x, y, seg_row, rows, lane, lt, pol_keep, sv, segs_base, wcarry)
     for (uint32_t vc = blockIdx.x * (SK_THREADS / 32) + (threadIdx.x >> 5); vc < nchunks; vc += nwarps) {
         uint32_t t = vc * chunk;
         const uint32_t t1 = min(t + chunk, nwt);

@@ -52,7 +52,51 @@ __global__ void add_u32_kernel(uint32_t *__restrict__ a, uint64_t n, uint32_t ad
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) a[i] += add;
 }
 
+// out[0] = max over e of (ind[e] & mask); out[1] != 0 when ptr[0..nptr] is not non-decreasing or leaves [0, n]
+__global__ void validate_kernel(const uint32_t *__restrict__ ind, uint64_t n, uint32_t mask, const uint32_t *__restrict__ ptr,
+                                uint64_t nptr, uint32_t *__restrict__ out)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, i0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t m = 0, bad = 0;
+    for (uint64_t e = i0; e < n; e += stride) m = max(m, ind[e] & mask);
+    if (ptr)
+        for (uint64_t c = i0; c < nptr; c += stride) bad |= (ptr[c] > ptr[c + 1]) || ((uint64_t)ptr[c + 1] > n);
+    m = __reduce_max_sync(0xFFFFFFFFu, m);
+    bad = __reduce_or_sync(0xFFFFFFFFu, bad);
+    if ((threadIdx.x & 31) == 0) {
+        if (m) atomicMax(out, m);
+        if (bad) atomicOr(out + 1, 1u);
+    }
+}
+
 }  // namespace
+
+// Index arrays that come from the caller are checked once before anything indexes with them: every
+// (ind[e] & mask) must be below `limit` and, when given, ptr[0..nptr] must be non-decreasing within [0, n].
+// A matrix that went through SparseMatrix::markRowStarts (bits 31 / 30 set, software/main.cpp:228-229) passed
+// with the default mask would otherwise scatter out of bounds on the device.
+int b2_validate_indices(b200spmv_ctx *ctx, const uint32_t *d_ind, uint64_t n, uint32_t mask, uint32_t limit,
+                        const uint32_t *d_ptr, uint64_t nptr, cudaStream_t s)
+{
+    uint32_t *d_out = nullptr, h[2] = {0, 0};
+    B2_TRY(b2_alloc(ctx, &d_out, 2));
+    cudaError_t e = cudaMemsetAsync(d_out, 0, 8, s);
+    const uint64_t work = std::max<uint64_t>(n, nptr);
+    validate_kernel<<<(unsigned)std::min<uint64_t>(std::max<uint64_t>(b2_div_up(work, 256), 1), (uint64_t)ctx->sms * 32), 256, 0, s>>>(
+        d_ind, n, mask, d_ptr, nptr, d_out);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_out, 8, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    b2_free(d_out);
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; return B200SPMV_ECUDA; }
+    if (h[1]) return b2_fail(ctx, B200SPMV_EINVAL, "pointer array is not non-decreasing within [0, nnz]");
+    if (h[0] >= limit) {
+        char buf[256];
+        snprintf(buf, sizeof buf, "index %u (after index_mask 0x%08X) is out of range [0, %u): marked indices "
+                 "(SparseMatrix::markRowStarts sets bits 31/30) need index_mask 0x3FFFFFFF", h[0], mask, limit);
+        return b2_fail(ctx, B200SPMV_EINVAL, buf);
+    }
+    return 0;
+}
 
 // rows that hold at least one of the n entries (bitmap + popcount); the slab heuristic counts entries per
 // NON-EMPTY row: the empty rows of a skewed matrix cost the kernels nothing

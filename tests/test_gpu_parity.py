@@ -185,6 +185,36 @@ def test_marked_matrix_needs_index_mask(b2, eng, oracle):
     assert y.tobytes() == golden.tobytes()
 
 
+def test_unchecked_indices_are_rejected(b2, eng, oracle):
+    """Caller-supplied index arrays are validated on the device before anything indexes with them:
+    marked row indices (bits 31 / 30, SparseMatrix.cpp:64) passed with the default mask, a row index >= rows, a
+    column pointer that is not non-decreasing, and marked / out-of-range indices into the row-mark entry points
+    all give B200SPMV_EINVAL (-1) instead of out-of-bounds device atomics; the context stays usable."""
+    m = H.load_matrix_dir(os.path.join(H.MATRICES, "circuit204"))
+    vals = m.data_raw.view(np.float64)
+    marked = m.rowind.copy()
+    oracle.lib.oracle_mark_row_starts(H.C.c_uint32(m.rows), H.C.c_uint32(m.nnz), H.ptr(marked), H.C.c_int(0), H.C.c_int(31))
+    with pytest.raises(b2.B200Error, match="index_mask"):
+        eng.setup_csc(m.rows, m.cols, m.colptr, marked, vals, b2.F64)
+    big = m.rowind.copy()
+    big[m.nnz // 2] = m.rows
+    with pytest.raises(b2.B200Error, match="-1"):
+        eng.setup_csc(m.rows, m.cols, m.colptr, big, vals, b2.F64)
+    cp = m.colptr.copy()
+    cp[5], cp[6] = cp[6] + 1, cp[5]
+    with pytest.raises(b2.B200Error, match="non-decreasing"):
+        eng.setup_csc(m.rows, m.cols, cp, m.rowind, vals, b2.F64)
+    with pytest.raises(b2.B200Error, match="-1"):
+        eng.mark_row_starts(m.rows, big.copy(), 0, 31)
+    with pytest.raises(b2.B200Error, match="-1"):
+        eng.max_alive(m.rows - 1, m.rowind.copy() | np.uint32(m.rows - 1))
+    # and the same context still works
+    eng.setup_csc(m.rows, m.cols, m.colptr, marked, vals, b2.F64, index_mask=0x3FFFFFFF)
+    golden = np.fromfile(os.path.join(H.MATRICES, "circuit204", "golden.bin"), dtype="<f8")
+    y = eng.exec(np.ones(m.cols), np.zeros(m.rows), b2.ACCUMULATE | b2.STRICT_ORDER)
+    assert y.tobytes() == golden.tobytes()
+
+
 def test_error_behaviour(b2, eng):
     m = H.load_matrix_dir(os.path.join(H.MATRICES, "i64"))
     x, y = np.ones(64), np.zeros(64)

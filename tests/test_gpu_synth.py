@@ -241,3 +241,39 @@ def test_exec_download_pipeline(b2, kind, rows, npr, slabs, dtype, kernel):
             assert np.allclose(y, y_in + dev, rtol=0, atol=1e-9)
         assert np.allclose(dev, want, rtol=0, atol=1e-9)
     e.close()
+
+
+@pytest.mark.parametrize("dtype", ["u64", "f64"])
+@pytest.mark.parametrize("pin", [0, 1])
+def test_exec_sliced_x_upload(b2, dtype, pin):
+    """b200spmv_exec with x >= 8 MB and several slabs uploads x slab slice by slab slice on the copy stream and the
+    kernels of slab s wait only for slice s (api.cu, ev_slab) -- the path bench.py's e2e number runs through
+    (ADVICE round 1).  2^21 columns, 3 forced slabs, pageable and page-locked-in-place host vectors, flags 0 /
+    ACCUMULATE / NO_PERSIST, a DIFFERENT x every repetition (a kernel that started before its slice had landed
+    would read the previous x): u64 bit-equal to the strict device-resident result, f64 within the per-row bound
+    2 n 2^-53 sum|a x| (+ the starting y), n = 4."""
+    rows = 1 << 21
+    e = b2.Engine(0)
+    e.set_option("slabs", 3)
+    e.set_option("pin_host", pin)
+    e.setup_synthetic(0, rows, rows, 4, SEED, DT(b2, dtype))
+    assert e.stat("slabs") == 3
+    npdt = np.uint64 if dtype == "u64" else np.float64
+    for rep, flags in enumerate((0, b2.ACCUMULATE, b2.NO_PERSIST, b2.ACCUMULATE | b2.NO_PERSIST, 0, b2.ACCUMULATE)):
+        x = H.make_x(rows, dtype, "rand", 500 + rep)
+        y0 = H.make_x(rows, dtype, "rand", 600 + rep)
+        # oracle for this x: the strict kernel on device-resident vectors (itself pinned against the reference)
+        e.set_x(x)
+        e.set_y(y0 if flags & b2.ACCUMULATE else np.zeros(rows, dtype=npdt))
+        e.exec_device(1, b2.STRICT_ORDER | (flags & b2.ACCUMULATE))
+        want = e.get_y()
+        e.set_x(np.zeros(rows, dtype=npdt))  # exec must bring its own x
+        y = y0.copy()
+        e.exec(x, y, flags)
+        if dtype == "u64":
+            assert y.tobytes() == want.tobytes(), (rep, flags)
+        else:
+            # |a| < 1, |x| < 1, 4 entries per row: sum|a x| < 4
+            bound = 2.0 * 5 * EPS * (4.0 + np.abs(y0))
+            assert (np.abs(y - want) <= bound).all(), (rep, flags, float(np.abs(y - want).max()))
+    e.close()
