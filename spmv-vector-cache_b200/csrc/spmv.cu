@@ -253,9 +253,6 @@ constexpr int SK_THREADS = 256;
 constexpr int WK_ENTRIES = 256;  // per warp step: 32 lanes x 8 entries
 constexpr int WK_PER_TILE = (int)(B2_FLAG_TILE / WK_ENTRIES);
 
-#ifndef B200SPMV_YPF
-#define B200SPMV_YPF 1  // 0: no L2 prefetch of y / seg_row ahead of the warp (A/B builds)
-#endif
 #ifndef B200SPMV_ABLATE
 #define B200SPMV_ABLATE 0  // measurement builds only (make ablate): 1 no y stores, 3 no row logic, 4 no gathers either
 #endif
@@ -267,6 +264,15 @@ __device__ __forceinline__ void stream_load(uint32_t (&c)[8], uint64_t (&p)[8], 
     ld256_u64(vp + 4, p + 4);
 }
 
+// Row id of the segment (non-empty row) with index seg; seg may run past the slab's last segment (prefetch for a
+// step that closes fewer rows): the table has rows + 1 entries per slab, anything past it reads as "no row".
+template <bool HAS_EMPTY>
+__device__ __forceinline__ uint32_t segment_row(const uint32_t *__restrict__ seg_row, uint32_t rows, uint32_t seg)
+{
+    if (!HAS_EMPTY) return seg;
+    return seg <= rows ? __ldg(seg_row + seg) : NO_ROW;
+}
+
 // One warp step: 256 consecutive entries, c / p = this lane's 8 column ids (flag in bit 31) and values.
 // segs_base = row-start flags before the step's first entry, wcarry = partial sum of the row open on entry;
 // both are advanced to the end of the step.
@@ -274,15 +280,17 @@ __device__ __forceinline__ void stream_load(uint32_t (&c)[8], uint64_t (&p)[8], 
 // Every flag closes the row before it.  The sums of the rows a step closes are collected in a warp-private
 // shared-memory strip sv[] -- slot j = j-th row closed by the step, i.e. segment segs_base - 1 + j -- and written
 // out by lane j: consecutive segments are (nearly) consecutive rows, so y is read and written with ONE coalesced
-// load and ONE coalesced store per 32 closed rows.  (Round-2 measurement: letting every closing thread update y
-// itself, by load/add/store or by red.global.add, costs an L2 request per row; on a gather-bound matrix the
-// SM's L2 request port is the bottleneck, and those requests took 8 % (uniform) to 17 % (band) of the step.)
-// The row ids and the old y of the first 32 closed rows are requested before the gathers go out.
-template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, bool Y_PF>
+// load and ONE coalesced store per 32 closed rows instead of one request per row.
+// The step is one stage of a software pipeline over the warp's chunk: row_n / y_n arrive holding the row id and
+// the old y of slot `lane` of THIS step (requested a whole step ago), and leave holding those of the next step
+// -- its first segment is known as soon as this step's flags are counted.  ncu on the version that looked the row
+// ids up inside the step: 20 % of all warp time waiting for the row-id table and as much again for y, with the
+// SM's L2 request port -- the real limit of a gather-bound matrix -- only 71 % busy.
+template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY>
 __device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p)[8], const uint64_t *__restrict__ x,
                                             uint64_t *__restrict__ y, const uint32_t *__restrict__ seg_row, uint32_t rows,
                                             int lane, uint32_t lt, uint64_t pol_keep, uint64_t *__restrict__ sv,
-                                            uint32_t &segs_base, uint64_t &wcarry)
+                                            uint32_t &segs_base, uint64_t &wcarry, uint32_t &row_n, uint64_t &y_n)
 {
     constexpr int ABL = B200SPMV_ABLATE;
     uint64_t xv[8];
@@ -308,31 +316,15 @@ __device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p
         warp_flags += __popc(bal_b) << bit;
     }
     const uint32_t bal = __ballot_sync(0xffffffffu, nfl != 0);
-    // write-out duty of this lane: the lane-th row the step closes (slot 0 of the very first step of a slab closes
-    // nothing: no row precedes the first flag)
-    const uint32_t my_seg = segs_base + (uint32_t)lane - 1u;
-    uint32_t my_row = NO_ROW;
-    if ((uint32_t)lane < warp_flags && my_seg != 0xFFFFFFFFu) {
-        my_row = HAS_EMPTY ? __ldg(seg_row + my_seg) : my_seg;
-        if (my_row >= rows) my_row = NO_ROW;
-    }
+    // next step's slot `lane`: segment (segs_base + warp_flags) - 1 + lane.  Its row id is requested now and its y
+    // at the end of this step; both are consumed at the end of the next one.
+    const uint32_t next_seg = segs_base + warp_flags + (uint32_t)lane - 1u;
+    const uint32_t row_next = next_seg != 0xFFFFFFFFu ? segment_row<HAS_EMPTY>(seg_row, rows, next_seg) : NO_ROW;
 #pragma unroll
     for (int i = 0; i < 8; i++) xv[i] = load_x<PERSIST>(x, c[i] & 0x7FFFFFFFu, pol_keep);
-    uint64_t y_old = 0;
-    if (READ_Y && my_row != NO_ROW) y_old = y[my_row];
-    // A warp walks its rows in ascending order, warp_flags of them per step.  y (and the row-id table) of the rows
-    // three steps ahead are pulled into L2 now: otherwise each step waits for a DRAM round trip of its y_old (and,
-    // before it, of its seg_row line) that is longer than the whole gather phase (ncu, round 2: long-scoreboard
-    // stalls with the L2 request port only 71 % busy).
-    if (Y_PF) {
-        const uint32_t ahead = segs_base + 3u * warp_flags;  // segment index ~3 steps ahead
-        if (HAS_EMPTY && lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(seg_row + min(ahead, rows)));
-        if (READ_Y) {
-            const uint32_t r0 = __shfl_sync(0xffffffffu, my_row, 0);  // first row this step closes
-            const uint64_t r = (uint64_t)r0 + 3u * warp_flags + 16u * (uint32_t)lane;
-            if (r0 != NO_ROW && 16u * (uint32_t)lane < warp_flags + 16u && r < rows) asm volatile("prefetch.global.L2 [%0];" ::"l"(y + r));
-        }
-    }
+    // write-out duty of this lane: the lane-th row the step closes
+    const uint32_t my_row = ((uint32_t)lane < warp_flags && row_n < rows) ? row_n : NO_ROW;
+    const uint64_t y_old = y_n;
 
     // branch-free sequential pass: head = sum before my first flag, acc = sum after my last flag; the rows that
     // begin and end inside my 8 entries go straight to their slots
@@ -376,7 +368,7 @@ __device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p
         if (ABL >= 1) wcarry ^= v; else y[my_row] = v;
     }
     for (uint32_t j = 32u + (uint32_t)lane; j < warp_flags; j += 32u) {  // short rows: more than 32 closed in one step
-        uint32_t row = HAS_EMPTY ? __ldg(seg_row + segs_base + j - 1u) : segs_base + j - 1u;
+        const uint32_t row = segment_row<HAS_EMPTY>(seg_row, rows, segs_base + j - 1u);
         if (row < rows) {
             const uint64_t v = READ_Y ? Semi<DT>::add(y[row], sv[j]) : sv[j];
             if (ABL >= 1) wcarry ^= v; else y[row] = v;
@@ -385,6 +377,8 @@ __device__ __forceinline__ void stream_step(const uint32_t (&c)[8], uint64_t (&p
     __syncwarp();  // sv is rewritten by the next step
     wcarry = bal ? s31 : Semi<DT>::add(wcarry, s31);
     segs_base += warp_flags;
+    row_n = row_next;
+    if (READ_Y) y_n = row_next < rows ? y[row_next] : 0ull;
 }
 
 // nwt = warp steps (256 entries) of the slab, cut into nchunks chunks of `chunk` steps; warp w of the grid takes
@@ -410,12 +404,16 @@ spmv_stream_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restri
         asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" ::"l"(colind + e), "r"(WK_ENTRIES * 4u), "l"(pol_stream) : "memory"); \
     }
 #define B2_STREAM_STEP(C, P) \
-    stream_step<DT, PERSIST, READ_Y, HAS_EMPTY, B200SPMV_YPF != 0>(C, P, x, y, seg_row, rows, lane, lt, pol_keep, sv, segs_base, wcarry)
+    stream_step<DT, PERSIST, READ_Y, HAS_EMPTY>(C, P, x, y, seg_row, rows, lane, lt, pol_keep, sv, segs_base, wcarry, row_n, y_n)
     for (uint32_t vc = blockIdx.x * (SK_THREADS / 32) + (threadIdx.x >> 5); vc < nchunks; vc += nwarps) {
         uint32_t t = vc * chunk;
         const uint32_t t1 = min(t + chunk, nwt);
         uint32_t segs_base = __ldg(warp_seg + t);
         uint64_t wcarry = 0;
+        // pipeline prologue: row id and old y of slot `lane` of the first step
+        const uint32_t first_seg = segs_base + (uint32_t)lane - 1u;
+        uint32_t row_n = first_seg != 0xFFFFFFFFu ? segment_row<HAS_EMPTY>(seg_row, rows, first_seg) : NO_ROW;
+        uint64_t y_n = (READ_Y && row_n < rows) ? y[row_n] : 0ull;
         const uint32_t *cp = colind + (uint64_t)t * WK_ENTRIES + lane * 8;
         const uint64_t *vp = vals + (uint64_t)t * WK_ENTRIES + lane * 8;
         uint32_t ca[8];

@@ -259,8 +259,12 @@ def test_exec_sliced_x_upload(b2, dtype, pin):
     e.setup_synthetic(0, rows, rows, 4, SEED, DT(b2, dtype))
     assert e.stat("slabs") == 3
     npdt = np.uint64 if dtype == "u64" else np.float64
+    # the SAME host buffers for every repetition, refilled in place: option pin_host page-locks them where they lie
+    # and requires them to outlive the context's use (SpMV objects keep their vectors for life, software/SpMV.h:31-33)
+    x = np.zeros(rows, dtype=npdt)
+    y = np.zeros(rows, dtype=npdt)
     for rep, flags in enumerate((0, b2.ACCUMULATE, b2.NO_PERSIST, b2.ACCUMULATE | b2.NO_PERSIST, 0, b2.ACCUMULATE)):
-        x = H.make_x(rows, dtype, "rand", 500 + rep)
+        x[:] = H.make_x(rows, dtype, "rand", 500 + rep)
         y0 = H.make_x(rows, dtype, "rand", 600 + rep)
         # oracle for this x: the strict kernel on device-resident vectors (itself pinned against the reference)
         e.set_x(x)
@@ -268,7 +272,7 @@ def test_exec_sliced_x_upload(b2, dtype, pin):
         e.exec_device(1, b2.STRICT_ORDER | (flags & b2.ACCUMULATE))
         want = e.get_y()
         e.set_x(np.zeros(rows, dtype=npdt))  # exec must bring its own x
-        y = y0.copy()
+        y[:] = y0
         e.exec(x, y, flags)
         if dtype == "u64":
             assert y.tobytes() == want.tobytes(), (rep, flags)

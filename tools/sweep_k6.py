@@ -36,7 +36,7 @@ args = ap.parse_args()
 
 # (name, kind, rows, npr, slabs list)
 WORK = [
-    ("uniform C3", 0, 1 << 24, 32, [3, 4, 5]),
+    ("uniform C3", 0, 1 << 24, 32, [3, 4]),
     ("band16", 3, 1 << 24, 16, [1, 3]),
     ("banded11+5", 2, 1 << 24, 5, [1, 3]),
     ("rmat16M", 1, 1 << 24, 32, [0]),
@@ -51,9 +51,7 @@ VARIANTS = [
     ("k3", {"kernel": 3}),
     ("k6 db occ2", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1}),
     ("k6 nodb occ3", {"kernel": 6, "stream_db": 0, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1}),
-    ("k6 nodb occ3 v4", {"kernel": 6, "stream_db": 0, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 4}),
     ("k6 nodb occ3 pf1", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1}),
-    ("k6 nodb occ3 pf2", {"kernel": 6, "stream_db": 0, "stream_pf": 2, "stream_occ": 0, "stream_vchunks": 1}),
     ("k6 db occ2 pf2", {"kernel": 6, "stream_db": 1, "stream_pf": 2, "stream_occ": 0, "stream_vchunks": 1}),
     ("k6 db occ2 nopersist", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1, "_flags": 4}),
     ("k6 db occ2 dcsr0", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1, "dcsr_x16": 0}),
