@@ -192,120 +192,206 @@ def run_reference(args):
     print(json.dumps(line))
 
 
-def run_ours(args):
-    import numpy as np
-    import torch
-    import b200spmv as b2
+class Job:
+    """Rendezvous + helpers shared by the headline measurement and the other configs of the same launch."""
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        import torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    def __init__(self, args):
+        import numpy as np
+        import torch
+        import b200spmv as b2
+        self.np, self.torch, self.b2, self.args = np, torch, b2, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            torch.cuda.set_device(self.local)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist = dist
+
+    def barrier(self):
+        if self.dist:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, v, op="max"):
+        if not self.dist:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.MIN)
+        return float(t.item())
+
+    def engine(self, comm, exchange=None, shard=True):
+        """A context on this rank's GPU.  comm: attach the NCCL communicator (needed by the power iteration);
+        otherwise the rank takes its row block by option (a single SpMV needs no collective)."""
+        b2, args = self.b2, self.args
+        eng = b2.Engine(self.local)
+        if self.world > 1 and shard:
+            if comm:
+                uid = self.torch.zeros(128, dtype=self.torch.uint8, device="cuda")
+                if self.rank == 0:
+                    uid.copy_(self.torch.frombuffer(bytearray(b2.comm_unique_id()), dtype=self.torch.uint8))
+                self.dist.broadcast(uid, 0)
+                eng.comm_init(self.rank, self.world, bytes(uid.cpu().numpy().tobytes()))
+            else:
+                eng.set_option("world", self.world)
+                eng.set_option("rank", self.rank)
+        if args.shard:  # one rank's row block of a W-way split, alone on this GPU (tuning runs; no collective)
+            r_, w_ = (int(v) for v in args.shard.split("/"))
+            eng.set_option("world", w_)
+            eng.set_option("rank", r_)
+        if args.dcsr is not None:
+            eng.set_option("dcsr_x16", args.dcsr)
+        if args.slabs:
+            eng.set_option("slabs", args.slabs)
+        if args.kernel:
+            eng.set_option("kernel", args.kernel)
+        for opt in ("stream_db", "stream_pf", "stream_occ", "stream_vchunks"):
+            if getattr(args, opt) is not None:
+                eng.set_option(opt, getattr(args, opt))
+        if args.prefetch is not None:
+            eng.set_option("prefetch_tiles", args.prefetch)
+        if args.graph is not None:
+            eng.set_option("graph", args.graph)
+        if args.own_slabs:
+            eng.set_option("own_slabs", 1)
+        if args.prefetch_x is not None:
+            eng.set_option("prefetch_x", args.prefetch_x)
+        if exchange in ("pull", "overlap") and self.world > 1 and shard and not args.shard:
+            # slabs aligned with the ranks' x blocks: the exchange of the other blocks runs under the own-block slabs
+            eng.set_option("own_slabs", 1)
+            eng.set_option("exchange", 2 if exchange == "pull" else 1)
+            if args.pull_streams:
+                eng.set_option("pull_streams", args.pull_streams)
+        return eng
+
+    # ---- parity inside the bench run (VERDICT round 1, next 2): no oracle here, the CUDA paths against each other ----
+    def parity(self, kind, rows, cols, npr, power, exchange):
+        """u64 twin of the timed matrix (same generator, same sparsity structure, same kernels, wrapping integer
+        arithmetic so every order of summation gives the same bits): the throughput kernels against the strict
+        row-sequential kernel on every row of this rank's block, y = A*x and y += A*x; for the power iteration
+        3 distributed steps against 3 steps of a private single-GPU replica of the whole matrix (the replicated x
+        must be bit-equal on every rank).  All ranks' verdicts are min-reduced."""
+        np, b2 = self.np, self.b2
+        ok, checked = True, 0
+        e = self.engine(comm=power, exchange=exchange)
+        e.setup_synthetic(kind, rows, cols, npr, SEED, b2.U64)
+        e.fill_x_synthetic(SEED + 1)
+        rb, re = e.stat("row_begin"), e.stat("row_end")
+        e.fill_y_zero()
+        e.exec_device(1, 0)
+        ya = e.get_y()[rb:re].copy()
+        e.exec_device(1, b2.ACCUMULATE)          # y += A*x on top: 2 * A*x mod 2^64
+        yb = e.get_y()[rb:re].copy()
+        e.exec_device(1, b2.STRICT_ORDER)
+        ys = e.get_y()[rb:re].copy()
+        ok = ok and ya.tobytes() == ys.tobytes() and yb.tobytes() == (ys + ys).tobytes()
+        checked += re - rb
+        detail = {"spmv_u64_vs_strict": bool(ya.tobytes() == ys.tobytes()), "accumulate": bool(yb.tobytes() == (ys + ys).tobytes())}
+        if power and self.world > 1:
+            e.power_iterate(3, False, 0)
+            xd = e.get_x()
+            e.close()
+            e = self.engine(comm=False, shard=False)  # the whole matrix on this GPU alone
+            e.setup_synthetic(kind, rows, cols, npr, SEED, b2.U64)
+            e.power_iterate(3, False, 0)
+            same = xd.tobytes() == e.get_x().tobytes()
+            detail["power_3_steps_vs_single_gpu"] = bool(same)
+            ok = ok and same
+        e.close()
+        ok_all = self.reduce(1.0 if ok else 0.0, "min") == 1.0
+        rows_all = int(self.reduce(float(checked), "max")) if self.world == 1 else rows
+        return {"ok": bool(ok_all), "checked_rows": rows_all, "how": "u64 twin of the same matrix: throughput kernels == strict "
+                "row-sequential kernel bit for bit on every row (y = A*x and y += A*x)" +
+                ("; 3 distributed power-iteration steps == single-GPU replica (replicated x, every rank)" if power and self.world > 1 else ""),
+                "rank0": detail}
+
+    # ---- one config, device-resident ---------------------------------------------------------------------------
+    def measure(self, workload, steps, warmup, flags, exchange="pull", power=None, rows=None, cols=None, npr=None):
+        """-> dict(value, ms_per_step, roofline, ...) for `workload` at this launch's N; leaves nothing allocated."""
+        np, b2, args = self.np, self.b2, self.args
+        kind, rows_d, npr_d, desc = WORKLOADS[workload]
+        rows = rows or rows_d
+        cols = cols or rows
+        npr = npr or npr_d
+        power = (workload == "banded-power" and not args.shard and not args.no_power) if power is None else power
+        eng = self.engine(comm=True, exchange=exchange if power else None)
+        t0 = time.perf_counter()
+        eng.setup_synthetic(kind, rows, cols, npr, SEED, b2.F64)
+        setup_s = time.perf_counter() - t0
+        nnz, lnnz, lrows = eng.stat("nz"), eng.stat("local_nz"), eng.stat("local_rows")
+        eng.fill_x_synthetic(SEED + 1)
+        eng.fill_y_zero()
+        out = {"desc": desc, "rows": rows, "cols": cols, "nnz": nnz, "setup_s": setup_s, "power": power}
+        if power:
+            eng.power_iterate(max(warmup, 3), False, flags & ~b2.ACCUMULATE)
+        else:
+            eng.exec_device(max(warmup, 3), flags)
+        self.barrier()
+        launches0 = eng.stat("launches")
+        if power:
+            ms_total, out["last_norm"] = eng.power_iterate(steps, True, flags & ~b2.ACCUMULATE)
+        else:
+            ms = eng.exec_device(steps, flags)  # CUDA events on the launching stream, one pair per step
+            ms_total = float(ms.sum())
+            out["step_stats"] = {"ms_best": float(ms.min()), "ms_median": float(np.median(ms))}  # this rank's steps (SURVEY 8d)
+        self.barrier()
+        out["launches"] = eng.stat("launches") - launches0
+        t_dev = self.reduce(ms_total) * 1e-3
+        out["t_dev"] = t_dev
+        out["value"] = (lnnz if args.shard else nnz) * steps / t_dev / 1e9
+        out["ms_per_step"] = 1e3 * t_dev / steps
+        if power and self.world > 1:
+            out["x_exchange_ms_last_step"] = eng.stat("xchgtime_ns") * 1e-6
+            out["exchange"] = ["NCCL all-gather after the step", "NCCL all-gather under the own-block slabs",
+                               "peer pulls block by block under the slabs"][eng.stat("exchange_mode")]
+        # the dominant kernel alone (roofline), same workload, events around each launch
+        eng.set_option("profile", 1)
+        psteps = min(steps, 20)
+        eng.exec_device(psteps, flags)
+        k_ns, k_n = eng.stat("merge_kernel_ns"), eng.stat("merge_kernel_launches")
+        slabs = eng.stat("slabs")
+        if args.per_slab:
+            out["per_slab"] = [{"ms": round(eng.stat("slab_ns_%d" % i) * 1e-6 / psteps, 4), "nnz": eng.stat("slab_nnz_%d" % i),
+                                "nonempty_rows": eng.stat("slab_rows_%d" % i), "longest_row": eng.stat("slab_maxrow_%d" % i)}
+                               for i in range(slabs)]
+        eng.set_option("profile", 0)
+        mode = eng.stat("mode")
+        # the strict kernel has no per-launch bracket: its step time is the kernel time (one launch per slab)
+        kernel_ms = k_ns * 1e-6 / k_n * slabs if k_n else 1e3 * t_dev / steps
+        peak, peak_src = measured_peak_gbs()
+        alg_local = 12 * lnnz + 4 * (lrows + 1) + 8 * cols + 8 * lrows
+        achieved = alg_local / (kernel_ms * 1e-3) / 1e9
+        traffic, traffic_src = recorded_traffic(workload, rows, cols, slabs, mode, self.world, flags)
+        out.update(slabs=slabs, mode=mode, lrows=lrows, lnnz=lnnz)
+        out["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                           "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                           "kernel": KERNEL_NAMES.get(mode, "?"), "kernel_ms_per_step": kernel_ms,
+                           "kernel_launches_per_step": slabs, "algorithmic_bytes_per_step": alg_local,
+                           "frac_of_8TBs_nominal": achieved / 8000.0}
+        out["eng"] = eng
+        return out
+
+
+def run_ours(args):
+    job = Job(args)
+    np, torch, b2 = job.np, job.torch, job.b2
+    rank, world, local = job.rank, job.world, job.local
     kind, rows, npr, desc = WORKLOADS[args.workload]
-    if args.rows:
-        rows = args.rows
+    rows = args.rows or rows
     cols = args.cols or rows
-    if args.npr:
-        npr = args.npr
+    npr = args.npr or npr
     flags = 0 if args.overwrite else b2.ACCUMULATE
     if args.no_persist:
         flags |= b2.NO_PERSIST
     if args.strict:
         flags |= b2.STRICT_ORDER
 
-    eng = b2.Engine(local)
-    if world > 1:
-        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            uid.copy_(torch.frombuffer(bytearray(b2.comm_unique_id()), dtype=torch.uint8))
-        dist.broadcast(uid, 0)
-        eng.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
-    if args.shard:  # one rank's row block of a W-way split, alone on this GPU (tuning runs; no collective)
-        r_, w_ = (int(v) for v in args.shard.split("/"))
-        eng.set_option("world", w_)
-        eng.set_option("rank", r_)
-    if args.dcsr is not None:
-        eng.set_option("dcsr_x16", args.dcsr)
-    if args.slabs:
-        eng.set_option("slabs", args.slabs)
-    if args.kernel:
-        eng.set_option("kernel", args.kernel)
-    for opt in ("stream_db", "stream_pf", "stream_occ", "stream_vchunks"):
-        if getattr(args, opt) is not None:
-            eng.set_option(opt, getattr(args, opt))
-    if args.prefetch is not None:
-        eng.set_option("prefetch_tiles", args.prefetch)
-    if args.graph is not None:
-        eng.set_option("graph", args.graph)
-    if args.own_slabs:
-        eng.set_option("own_slabs", 1)
-    if args.prefetch_x is not None:
-        eng.set_option("prefetch_x", args.prefetch_x)
-    if args.workload == "banded-power" and world > 1 and not args.shard and args.exchange != "nccl":
-        # slabs aligned with the ranks' x blocks: the exchange of the other blocks runs under the own-block slabs
-        eng.set_option("own_slabs", 1)
-        eng.set_option("exchange", 2 if args.exchange == "pull" else 1)
-        if args.pull_streams:
-            eng.set_option("pull_streams", args.pull_streams)
-    t0 = time.perf_counter()
-    eng.setup_synthetic(kind, rows, cols, npr, SEED, b2.F64)
-    setup_s = time.perf_counter() - t0
-    nnz, lnnz, lrows = eng.stat("nz"), eng.stat("local_nz"), eng.stat("local_rows")
-    eng.fill_x_synthetic(SEED + 1)
-    eng.fill_y_zero()
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    power = args.workload == "banded-power" and not args.shard and not args.no_power
-    step_stats = {}
     sampler = ClockSampler(local)
-    # ---- device-resident timing: W warm-up, then exactly K steps --------------------------
-    if power:
-        eng.power_iterate(max(args.warmup, 3), False, flags & ~b2.ACCUMULATE)
-    else:
-        eng.exec_device(max(args.warmup, 3), flags)
-    barrier()
-    launches0 = eng.stat("launches")
     sampler.start()
-    if power:
-        ms_total, last_norm = eng.power_iterate(args.steps, True, flags & ~b2.ACCUMULATE)
-    else:
-        ms = eng.exec_device(args.steps, flags)  # CUDA events on the launching stream, one pair per step
-        ms_total = float(ms.sum())
-        step_stats = {"ms_best": float(ms.min()), "ms_median": float(np.median(ms))}  # this rank's steps
-    barrier()
-    launches = eng.stat("launches") - launches0
-    t_dev = max_over_ranks(ms_total) * 1e-3
-    value = (lnnz if args.shard else nnz) * args.steps / t_dev / 1e9
-
-    # ---- the dominant kernel alone (roofline), same workload, events around each launch ----
-    eng.set_option("profile", 1)
-    eng.exec_device(args.steps, flags)
-    k_ns, k_n = eng.stat("merge_kernel_ns"), eng.stat("merge_kernel_launches")
-    slabs = eng.stat("slabs")
-    per_slab = [{"ms": round(eng.stat("slab_ns_%d" % i) * 1e-6 / args.steps, 4), "nnz": eng.stat("slab_nnz_%d" % i),
-                 "nonempty_rows": eng.stat("slab_rows_%d" % i), "longest_row": eng.stat("slab_maxrow_%d" % i)} for i in range(slabs)] if args.per_slab else None
-    eng.set_option("profile", 0)
-    eng_mode = eng.stat("mode")
-    traffic, traffic_src = recorded_traffic(args.workload, rows, cols, slabs, eng_mode, world, flags)
-    # the strict kernel has no per-launch bracket: its step time is the kernel time (one launch per slab)
-    kernel_ms_per_step = k_ns * 1e-6 / k_n * slabs if k_n else 1e3 * t_dev / args.steps
-    peak, peak_src = measured_peak_gbs()
-    alg_local = 12 * lnnz + 4 * (lrows + 1) + 8 * cols + 8 * lrows
-    achieved = alg_local / (kernel_ms_per_step * 1e-3) / 1e9
+    m = job.measure(args.workload, args.steps, args.warmup, flags, exchange=args.exchange, rows=rows, cols=cols, npr=npr)
+    eng, nnz, lrows, power, t_dev = m["eng"], m["nnz"], m["lrows"], m["power"], m["t_dev"]
 
     # ---- end to end through b200spmv_exec with pinned HOST vectors --------------------------
     dt = torch.float64
@@ -315,54 +401,92 @@ def run_ours(args):
     e2e_steps = min(args.steps, 50)
     for _ in range(3):
         eng.exec(xh.data_ptr(), yh.data_ptr(), flags)
-    barrier()
+    job.barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         eng.exec(xh.data_ptr(), yh.data_ptr(), flags)  # H2D x (+y), kernels, D2H y; blocking
     torch.cuda.synchronize()
-    t_e2e = max_over_ranks(time.perf_counter() - t0)
+    t_e2e = job.reduce(time.perf_counter() - t0)
     timeline = {k: round(eng.stat("exec_%s_ns" % k) * 1e-6, 3) for k in ("x_up", "y_up", "kernels", "done")}
-    barrier()
+    job.barrier()
     clocks = sampler.stop()
-    h2d = 8 * cols + (8 * lrows if flags & b2.ACCUMULATE else 0)
-    d2h = 8 * lrows
+    h2d, d2h = eng.stat("exec_h2d_bytes"), eng.stat("exec_d2h_bytes")  # per rank, counted from the copies b200spmv_exec issued
+    # spot-check of the end-to-end path: one more exec from a zeroed host y against the device-resident result of
+    # the same x (fp64, two re-associations of the same sums: |a|, |x| < 1, so 1e-9 absolute is ~1e5 ulp of slack
+    # on a 32-term sum yet far below any wrong or missing entry)
+    rb, re = eng.stat("row_begin"), eng.stat("row_end")
+    yh.zero_()
+    eng.exec(xh.data_ptr(), yh.data_ptr(), flags & ~b2.ACCUMULATE)
+    eng.exec_device(1, flags & ~b2.ACCUMULATE)
+    e2e_ok = bool(np.allclose(yh.numpy()[rb:re], eng.get_y()[rb:re], rtol=0, atol=1e-9))
+    e2e_ok = job.reduce(1.0 if e2e_ok else 0.0, "min") == 1.0
+    eng.close()
 
+    parity = None
+    if not args.no_parity:
+        parity = job.parity(kind, rows, cols, npr, power, args.exchange)
+        parity["e2e_exec_vs_device"] = e2e_ok
+
+    # ---- the other configs BASELINE.json names, at the same N (driver-visible C4 / C5) -------------------------
+    others = None
+    if args.workload == "uniform" and not args.no_others and not args.shard:
+        others = {}
+        specs = [("rmat", "rmat", 20, None)]
+        for ex in (("nccl", "pull") if world > 1 else ("pull",)):
+            specs.append(("banded_power" + ("_" + ex if world > 1 else ""), "banded-power", 100, ex))
+        for key, wl, k_steps, ex in specs:
+            try:
+                o = job.measure(wl, k_steps, 3, flags, exchange=ex or "pull")
+                o.pop("eng").close()
+                rec = {"workload": o["desc"], "value": o["value"], "unit": "GNNZ/s", "steps": k_steps, "ms_per_step": o["ms_per_step"],
+                       "rows": o["rows"], "nnz": o["nnz"], "slabs": o["slabs"], "setup_s": round(o["setup_s"], 2),
+                       "roofline": {k: o["roofline"][k] for k in ("achieved", "peak", "frac", "kernel", "kernel_ms_per_step", "algorithmic_bytes_per_step")}}
+                for k in ("x_exchange_ms_last_step", "exchange", "last_norm"):
+                    if k in o:
+                        rec[k] = o[k]
+                if not args.no_parity:
+                    kd, rw, nr, _ = WORKLOADS[wl]
+                    rec["parity"] = job.parity(kd, rw, rw, nr, o["power"], ex or "pull")
+                others[key] = rec
+            except Exception as exc:  # a config that does not fit or fails must not take the headline line with it
+                others[key] = {"error": "%s: %s" % (type(exc).__name__, exc)}
+
+    bad = (parity is not None and not parity["ok"]) or (others and any(not v.get("parity", {"ok": True})["ok"] for v in others.values()))
     if rank == 0:
         line = {
-            "metric": METRIC, "value": value, "unit": "GNNZ/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True,
+            "metric": METRIC, "value": m["value"], "unit": "GNNZ/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": m["ms_per_step"], "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": desc, "rows": rows, "cols": cols, "nnz": nnz, "seed": SEED,
+            "config": {"workload": m["desc"], "rows": rows, "cols": cols, "nnz": nnz, "seed": SEED,
                        "semantics": "y = A*x" if args.overwrite else "y += A*x (reference semantics)",
                        "partition": "nnz-balanced row blocks, no collective" if not power else
                                     "row blocks + x all-gather per step",
                        "l2": "inputs (%.1f GB) larger than L2; no flush" % (b_alg(nnz, rows, cols) / 1e9),
-                       "slabs": slabs, "persist_window": not args.no_persist, "setup_s": round(setup_s, 2),
-                       "setup_amortised_over_steps": int(round(setup_s / (t_dev / args.steps))), **step_stats,
-                       **({"x_exchange_ms_last_step": eng.stat("xchgtime_ns") * 1e-6, "exchange": ["NCCL all-gather after the step", "NCCL all-gather under the own-block slabs",
-                                        "peer pulls block by block under the slabs"][eng.stat("exchange_mode")]}
-                          if power and world > 1 else {}),
-                       **({"norm_after_last_step": last_norm} if power else {}),
-                       **({"per_slab": per_slab} if per_slab else {})},
+                       "slabs": m["slabs"], "persist_window": not args.no_persist, "setup_s": round(m["setup_s"], 2),
+                       "setup_amortised_over_steps": int(round(m["setup_s"] / (t_dev / args.steps))), **m.get("step_stats", {}),
+                       **({k: m[k] for k in ("x_exchange_ms_last_step", "exchange") if k in m}),
+                       **({"norm_after_last_step": m["last_norm"]} if power else {}),
+                       **({"per_slab": m["per_slab"]} if "per_slab" in m else {})},
             "gb_s_algorithmic": b_alg(nnz, rows, cols) * args.steps / t_dev / 1e9 if world == 1 else None,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
-                         "peak_source": peak_src,
-                         "kernel": KERNEL_NAMES.get(eng_mode, "?"), "kernel_ms_per_step": kernel_ms_per_step,
-                         "kernel_launches_per_step": slabs,
-                         "algorithmic_bytes_per_step": alg_local, "frac_of_8TBs_nominal": achieved / 8000.0},
+            "roofline": m["roofline"],
             "e2e": {"value": nnz * e2e_steps / t_e2e / 1e9, "unit": "GNNZ/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": 1e3 * t_e2e / e2e_steps,
+                    "d2h_bytes_per_step": d2h, "bytes_are": "per rank (rank 0)", "steps": e2e_steps, "ms_per_step": 1e3 * t_e2e / e2e_steps,
+                    **({"x_exchange": "each rank uploads 1/%d of x over PCIe, ncclAllGather over NVLink" % world} if world > 1 else {}),
                     "last_step_timeline_ms": timeline},
-            "gpu_launches": int(launches), "clocks": clocks,
+            "gpu_launches": int(m["launches"]), "clocks": clocks,
         }
+        if parity is not None:
+            line["parity"] = parity
+        if others is not None:
+            line["other_configs"] = others
         if world == 1 and not args.no_cpu:
             r = cpu_reference_sample(2, 1)
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line), flush=True)
-    eng.close()
-    if world > 1:
-        dist.destroy_process_group()
+    if job.dist:
+        job.dist.destroy_process_group()
+    if bad:
+        sys.exit(3)
 
 
 def main():
@@ -396,6 +520,8 @@ def main():
     ap.add_argument("--per-slab", action="store_true", help="add the kernel time of every slab to config")
     ap.add_argument("--strict", action="store_true", help="strict-order kernel (fp64 memcmp-equal to SoftwareSpMV)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-parity", action="store_true", help="skip the in-run parity checks")
+    ap.add_argument("--no-others", action="store_true", help="skip the other_configs (R-MAT, power iteration) of the default run")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -104,11 +104,23 @@ B200SPMV_API int b200spmv_setup_csc(b200spmv_ctx *ctx, uint32_t rows, uint32_t c
 B200SPMV_API int b200spmv_setup_synthetic(b200spmv_ctx *ctx, int kind, uint32_t rows, uint32_t cols,
                              uint32_t nnz_per_row, uint64_t seed, int dtype);
 
+/* Cross-check of a synthetic u64 matrix: recomputes A*x for this rank's rows straight from the generator's
+ * definition (csrc/synth_rng.h) -- R-MAT: one wrapping atomic add per edge, the other kinds one thread per row; no
+ * CSC, transpose, CSR or SpMV kernel involved -- with the x in HBM, and counts the rows where the y in HBM differs.
+ * For the full-size parity tests of the configs too large for a host oracle. */
+B200SPMV_API int b200spmv_check_synthetic_u64(b200spmv_ctx *ctx, int kind, uint32_t nnz_per_row, uint64_t seed,
+                                 uint64_t *mismatches);
+
 /* ---- exec: the SpMV::exec() contract (software/SpMV.h:12) ----------------------------- */
 /* H2D x (and y when accumulating), kernels, D2H y into the caller's vector; blocking.
  * x_host: cols elements, y_host: rows elements (this rank's row block when sharded:
  * see b200spmv_stat_u64 "row_begin"/"row_end"; y_host still points at element 0 of the
- * full vector). */
+ * full vector).
+ * With a communicator attached (b200spmv_comm_init, world > 1) and x >= 1 MB this is a COLLECTIVE call: every rank
+ * passes the same x, uploads only its 1/world of it over its own PCIe link and receives the rest from its peers
+ * over NVLink (ncclAllGather); all ranks must call it together.  Option "exec_gather" = 0 restores the
+ * every-rank-uploads-everything behaviour (no collective).  Stats exec_h2d_bytes / exec_d2h_bytes give what the
+ * last call moved over PCIe on this rank. */
 B200SPMV_API int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host, int flags);
 
 /* Device-resident variant for measurement: `iters` back-to-back SpMVs on the x / y already

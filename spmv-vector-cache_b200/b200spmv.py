@@ -22,7 +22,7 @@ EXPORTS = [
     "b200spmv_set_x", "b200spmv_set_y", "b200spmv_fill_x_synthetic", "b200spmv_fill_y_zero",
     "b200spmv_get_x", "b200spmv_get_y", "b200spmv_get_csr", "b200spmv_get_csc", "b200spmv_stat_u64",
     "b200spmv_comm_unique_id", "b200spmv_comm_init", "b200spmv_power_iterate",
-    "b200spmv_mark_row_starts", "b200spmv_max_alive", "b200spmv_max_col_span", "b200spmv_vector_cache_model",
+    "b200spmv_check_synthetic_u64", "b200spmv_mark_row_starts", "b200spmv_max_alive", "b200spmv_max_col_span", "b200spmv_vector_cache_model",
 ]
 
 _lib = None
@@ -103,6 +103,13 @@ class Engine:
         self._ck(self.L.b200spmv_setup_synthetic(self.ctx, C.c_int(kind), C.c_uint32(rows), C.c_uint32(cols),
                                                  C.c_uint32(npr), C.c_uint64(seed), C.c_int(dtype)),
                  "setup_synthetic")
+
+    def check_synthetic_u64(self, kind, npr, seed):
+        """rows of this rank's block where the y in HBM differs from A*x recomputed from the generator (u64)"""
+        out = C.c_uint64()
+        self._ck(self.L.b200spmv_check_synthetic_u64(self.ctx, C.c_int(kind), C.c_uint32(npr), C.c_uint64(seed), C.byref(out)),
+                 "check_synthetic_u64")
+        return out.value
 
     def exec(self, x, y, flags=ACCUMULATE):
         """y (+)= A*x on host vectors (numpy arrays or raw addresses), in place."""

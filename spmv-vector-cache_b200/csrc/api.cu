@@ -122,6 +122,7 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
         if (k == "world") { if (value < 1 || value > 64) return b2_fail(ctx, B200SPMV_EINVAL, "world must be 1..64"); ctx->world = (int)value; if (ctx->rank >= ctx->world) ctx->rank = 0; }
         else { if (value < 0 || value >= ctx->world) return b2_fail(ctx, B200SPMV_EINVAL, "rank must be 0..world-1"); ctx->rank = (int)value; }
     }
+    else if (k == "exec_gather") ctx->opt_exec_gather = value != 0;
     else if (k == "profile") { ctx->opt_profile = (int)value; ctx->merge_kernel_ns = 0; ctx->merge_kernel_launches = 0; ctx->prof_n = 0; memset(ctx->prof_slab_ns, 0, sizeof ctx->prof_slab_ns); }
     else return b2_fail(ctx, B200SPMV_EINVAL, "unknown option");
     return 0;
@@ -335,11 +336,23 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
     pin_in_place(ctx, 1, yh, (size_t)ctx->local_rows * 8);
     // x goes up slab slice by slab slice on the copy stream: the kernels of slab s only gather from slice s,
     // so they start as soon as it has landed (b2_spmv_launch waits on ev_slab[s]) while the rest still uploads
-    const bool sliced_x = ctx->slabs > 1 && !(flags & B200SPMV_STRICT_ORDER) && (size_t)ctx->cols * 8 >= (8u << 20);
+    // Several ranks with a communicator: every rank holds the same host x, so each uploads only its 1/world of the
+    // columns over its own PCIe link and the blocks are all-gathered over NVLink (ncclAllGather in place when the
+    // blocks are equal).  Otherwise every rank would pull the whole vector through PCIe: at 8 ranks 8 x 134 MB of
+    // host reads per step for one 134 MB vector, and the end-to-end rate FELL with the rank count (SCALE round 1).
+    const bool gather_x = ctx->comm && ctx->world > 1 && ctx->opt_exec_gather && (size_t)ctx->cols * 8 >= (1u << 20);
+    const bool sliced_x = !gather_x && ctx->slabs > 1 && !(flags & B200SPMV_STRICT_ORDER) && (size_t)ctx->cols * 8 >= (8u << 20);
     if (!ctx->ev_tl[0]) for (auto &e : ctx->ev_tl) B2_CHECK(ctx, cudaEventCreate(&e));
     B2_CHECK(ctx, cudaEventRecord(ctx->ev_tl[0], ctx->copy_stream));
     B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_tl[0], 0));
-    if (sliced_x) {
+    ctx->exec_h2d_bytes = (size_t)ctx->cols * 8;
+    if (gather_x) {
+        uint64_t lo, hi;
+        b2_exec_x_block(ctx, ctx->rank, &lo, &hi);
+        if (hi > lo) B2_CHECK(ctx, cudaMemcpyAsync((uint64_t *)ctx->d_x + lo, (const uint64_t *)x_host + lo, (hi - lo) * 8, cudaMemcpyHostToDevice, s));
+        B2_TRY(b2_exec_gather_x(ctx, s));
+        ctx->exec_h2d_bytes = (hi - lo) * 8;
+    } else if (sliced_x) {
         for (int sl = 0; sl < ctx->slabs; sl++) {
             const size_t c0 = ctx->h_slab_col[sl], c1 = ctx->h_slab_col[sl + 1];
             if (!ctx->ev_slab[sl]) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_slab[sl], cudaEventDisableTiming));
@@ -427,6 +440,8 @@ extern "C" int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_host
     ctx->spmvtime_ns = (uint64_t)((double)ms * 1e6);
     const uint64_t total = now_ns() - t0;
     ctx->xfertime_ns = total > ctx->spmvtime_ns ? total - ctx->spmvtime_ns : 0;
+    if (flags & B200SPMV_ACCUMULATE) ctx->exec_h2d_bytes += (uint64_t)ctx->local_rows * 8;
+    ctx->exec_d2h_bytes = (uint64_t)ctx->local_rows * 8;
     return 0;
 }
 
@@ -587,6 +602,8 @@ extern "C" int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *o
     else if (k == "exec_kernels_ns") *out = ctx->tl_ns[2];
     else if (k == "exec_done_ns") *out = ctx->tl_ns[3];
     else if (k == "exchange_mode") *out = (uint64_t)ctx->exchange_mode;
+    else if (k == "exec_h2d_bytes") *out = ctx->exec_h2d_bytes;
+    else if (k == "exec_d2h_bytes") *out = ctx->exec_d2h_bytes;
     else if (k.rfind("slab_ns_", 0) == 0 || k.rfind("slab_nnz_", 0) == 0 || k.rfind("slab_rows_", 0) == 0 || k.rfind("slab_maxrow_", 0) == 0) {
         const int i = atoi(k.c_str() + k.rfind('_') + 1);
         if (i < 0 || i >= ctx->slabs) return b2_fail(ctx, B200SPMV_EINVAL, "no such slab");

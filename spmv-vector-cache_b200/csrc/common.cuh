@@ -65,6 +65,7 @@ struct b200spmv_ctx {
     int opt_prefetch_x = 0;       // 1: stream each slab's slice of x into L2 (UBLKPF) before its kernel
     int opt_graph = 1;            // b200spmv_exec_device replays a captured CUDA graph of one step
     int opt_profile = 0;          // 1: bracket every merge-kernel launch with events (bench roofline)
+    int opt_exec_gather = 1;      // b200spmv_exec with a communicator: upload 1/world of x, all-gather the rest over NVLink
 
     // matrix
     bool ready = false;
@@ -128,6 +129,7 @@ struct b200spmv_ctx {
     cudaEvent_t ev_slab[64] = {nullptr};  // slice s of x has landed (b200spmv_exec uploads x slab by slab)
     bool wait_slab_events = false;
     cudaEvent_t ev_x0 = nullptr, ev_x1 = nullptr;  // around the x exchange of the last power-iteration step
+    uint64_t exec_h2d_bytes = 0, exec_d2h_bytes = 0;  // what the last b200spmv_exec moved over PCIe on this rank
     uint64_t xchgtime_ns = 0;
     // option pin_host: the caller's pageable x / y are page-locked in place (cudaHostRegister) the first time they
     // are seen and stay so until another pointer takes the slot or the context goes: SpMV objects keep their
@@ -233,6 +235,8 @@ int b2_synth_fill_x(b200spmv_ctx *ctx, uint64_t seed);
 int b2_comm_destroy(b200spmv_ctx *ctx);
 void b2_close_peers(b200spmv_ctx *ctx);
 int b2_shard_csc(b200spmv_ctx *ctx, uint32_t index_mask);
+void b2_exec_x_block(const b200spmv_ctx *ctx, int r, uint64_t *lo, uint64_t *hi);
+int b2_exec_gather_x(b200spmv_ctx *ctx, cudaStream_t s);
 
 // ---- device helpers --------------------------------------------------------------------
 #if defined(__CUDACC__)

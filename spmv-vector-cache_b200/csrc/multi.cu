@@ -261,6 +261,36 @@ static int allgather_x(b200spmv_ctx *ctx, cudaStream_t s)
     return 0;
 }
 
+// b200spmv_exec over several ranks: every rank has uploaded only columns [lo_r, hi_r) of x, lo_r = r * cols / world
+// (cut to whole 32-byte units), from the caller's host vector -- the same vector on every rank -- and the other
+// blocks arrive over NVLink instead of over every rank's own PCIe link.
+void b2_exec_x_block(const b200spmv_ctx *ctx, int r, uint64_t *lo, uint64_t *hi)
+{
+    *lo = ((uint64_t)ctx->cols * (uint64_t)r / (uint64_t)ctx->world) & ~3ull;
+    *hi = r + 1 == ctx->world ? ctx->cols : (((uint64_t)ctx->cols * (uint64_t)(r + 1) / (uint64_t)ctx->world) & ~3ull);
+}
+int b2_exec_gather_x(b200spmv_ctx *ctx, cudaStream_t s)
+{
+    if (ctx->world == 1 || !ctx->comm) return 0;
+    uint64_t *x = (uint64_t *)ctx->d_x;
+    uint64_t lo, hi;
+    b2_exec_x_block(ctx, 0, &lo, &hi);
+    const uint64_t per = hi - lo;
+    bool equal = g_nccl.allgather != nullptr;
+    for (int r = 0; r < ctx->world && equal; r++) { b2_exec_x_block(ctx, r, &lo, &hi); equal = hi - lo == per && lo == (uint64_t)r * per; }
+    if (equal) {
+        NCCL_TRY(ctx, g_nccl.allgather(x + (size_t)ctx->rank * per, x, (size_t)per, NCCL_UINT64, ctx->comm, s));
+        return 0;
+    }
+    NCCL_TRY(ctx, g_nccl.group_start());
+    for (int r = 0; r < ctx->world; r++) {
+        b2_exec_x_block(ctx, r, &lo, &hi);
+        if (hi > lo) NCCL_TRY(ctx, g_nccl.bcast(x + lo, x + lo, (size_t)(hi - lo), NCCL_UINT64, r, ctx->comm, s));
+    }
+    NCCL_TRY(ctx, g_nccl.group_end());
+    return 0;
+}
+
 // CUDA IPC mappings of the other ranks' x (one process per GPU on one node): handles travel through the
 // communicator.  Failure to map (no peer access between two GPUs) is not an error: the caller falls back to the
 // NCCL all-gather and stat "exchange_mode" says so.

@@ -86,7 +86,79 @@ __global__ void fill_x_kernel(uint64_t seed, uint64_t n, int u64, uint64_t *__re
         x[i] = synth_x_bits(seed, i, u64);
 }
 
+// ---- an independent statement of y = A*x for the synthetic matrices (u64, wrapping) ----------------------------
+// Straight off the generator's definition -- no CSC, no transpose, no CSR, none of the SpMV kernels: R-MAT adds
+// every edge of the rank's rows with an atomic (wrapping add is order-free), the row-generated kinds regenerate
+// each row in a thread.  Used by the full-size parity tests.
+__global__ void ref_rmat_kernel(uint64_t seed, int scale, uint64_t nedges, uint32_t rb, uint32_t re,
+                                const uint64_t *__restrict__ x, unsigned long long *__restrict__ yref)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nedges; e += stride) {
+        uint32_t r, c;
+        synth_rmat_edge(seed, e, scale, &r, &c);
+        if (r < rb || r >= re) continue;
+        atomicAdd(&yref[r - rb], (unsigned long long)(synth_value_bits(seed, e, 0, 1, SYNTH_RMAT, 0) * x[c]));
+    }
+}
+__global__ void ref_rows_kernel(int kind, uint64_t seed, uint32_t rows, uint32_t cols, uint32_t npr, uint32_t rb, uint32_t nlocal,
+                                const uint64_t *__restrict__ x, unsigned long long *__restrict__ yref)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nlocal) return;
+    uint32_t c[SYNTH_MAX_NPR + 2 * SYNTH_BAND_HALF + 1];
+    uint64_t v[SYNTH_MAX_NPR + 2 * SYNTH_BAND_HALF + 1];
+    const uint32_t n = synth_gen_row(kind, seed, rb + i, rows, cols, npr, 1, c, v);
+    uint64_t acc = 0;
+    for (uint32_t k = 0; k < n; k++) acc += v[k] * x[c[k]];
+    yref[i] = acc;
+}
+__global__ void count_diff_kernel(const uint64_t *__restrict__ a, const uint64_t *__restrict__ b, uint64_t n,
+                                  unsigned long long *__restrict__ out)
+{
+    unsigned c = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) c += a[i] != b[i];
+    c = __reduce_add_sync(0xFFFFFFFFu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
+}
+
 }  // namespace
+
+// mismatches = number of rows of this rank's block where the y in HBM differs from A*x recomputed from the
+// generator's definition with the x in HBM (u64 only: exact)
+extern "C" int b200spmv_check_synthetic_u64(b200spmv_ctx *ctx, int kind, uint32_t nnz_per_row, uint64_t seed, uint64_t *mismatches)
+{
+    if (!ctx || !mismatches) return B200SPMV_EINVAL;
+    if (!ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "call before setup");
+    if (ctx->dtype != B200SPMV_U64) return b2_fail(ctx, B200SPMV_EINVAL, "the generator cross-check is exact arithmetic: u64 only");
+    if (kind != SYNTH_RMAT && nnz_per_row > SYNTH_MAX_NPR) return b2_fail(ctx, B200SPMV_EINVAL, "nnz_per_row > 64");
+    B2_CHECK(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    unsigned long long *yref = nullptr, *cnt = nullptr, h = 0;
+    const uint64_t nl = ctx->local_rows;
+    B2_TRY(b2_alloc(ctx, &yref, nl + 1));
+    cnt = yref + nl;
+    B2_CHECK(ctx, cudaMemsetAsync(yref, 0, (nl + 1) * 8, s));
+    if (nl) {
+        if (kind == SYNTH_RMAT) {
+            int scale = 0;
+            while ((1ull << scale) < ctx->rows) scale++;
+            ref_rmat_kernel<<<ctx->sms * 16, 256, 0, s>>>(seed, scale, (uint64_t)ctx->rows * nnz_per_row, ctx->row_begin, ctx->row_end,
+                                                        (const uint64_t *)ctx->d_x, yref);
+        } else {
+            ref_rows_kernel<<<b2_div_up(nl, 128), 128, 0, s>>>(kind, seed, ctx->rows, ctx->cols, nnz_per_row, ctx->row_begin, (uint32_t)nl,
+                                                             (const uint64_t *)ctx->d_x, yref);
+        }
+        count_diff_kernel<<<ctx->sms * 8, 256, 0, s>>>((const uint64_t *)yref, (const uint64_t *)ctx->d_y + ctx->row_begin, nl, cnt);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&h, cnt, 8, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    b2_free(yref);
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; return B200SPMV_ECUDA; }
+    *mismatches = h;
+    return 0;
+}
 
 int b2_synth_fill_x(b200spmv_ctx *ctx, uint64_t seed)
 {

@@ -3,6 +3,7 @@
 
 #include <string.h>
 
+#include <chrono>
 #include <iostream>
 
 #include "../../include/b200spmv.h"
@@ -16,8 +17,10 @@ static const int kDtype = B200SPMV_F64;
 #endif
 
 CudaSpMV::CudaSpMV(SparseMatrix *A, SpMVData *x, SpMVData *y, const CudaSpMVOptions &opt)
-    : SpMV(A, x, y), m_ctx(0), m_opt(opt), m_ready(false), m_allocX(false), m_allocY(false), m_golden(-1), m_lastRc(0)
+    : SpMV(A, x, y), m_ctx(0), m_opt(opt), m_ready(false), m_allocX(false), m_allocY(false), m_golden(-1), m_lastRc(0),
+      m_cmsTime(0), m_maxAliveTime(0), m_maxColSpanTime(0), m_maxAlive(0), m_maxColSpan(0), m_vcDone(false)
 {
+    memset(m_vc, 0, sizeof m_vc);
     // default vectors like SoftwareSpMV.cpp:23-39: x = 1, y = 0, owned by this object
     if (m_x == 0) {
         m_x = new SpMVData[A->getCols()];
@@ -82,6 +85,51 @@ void CudaSpMV::compareGolden(SpMVData *golden)
     m_golden = memcmp(golden, m_y, (size_t)m_A->getRows() * sizeof(SpMVData)) != 0 ? 1 : 0;
 }
 
+static unsigned usSince(const chrono::steady_clock::time_point &t0)
+{
+    return (unsigned)chrono::duration_cast<chrono::microseconds>(chrono::steady_clock::now() - t0).count();
+}
+
+bool CudaSpMV::measurePreprocessingTimes()
+{
+    if (!ok()) return false;
+    const unsigned nz = m_A->getNz();
+    // a private copy of the row-index stream with any marker bits removed (clearRowMarkings, SparseMatrix.cpp:121-125)
+    vector<SpMVIndex> inds(m_A->getInds(), m_A->getInds() + nz);
+    for (unsigned i = 0; i < nz; i++) inds[i] &= 0x3FFFFFFFu;
+    chrono::steady_clock::time_point t0 = chrono::steady_clock::now();
+    m_lastRc = b200spmv_max_col_span(m_ctx, m_A->getCols(), nz, m_A->getIndPtrs(), &inds[0], &m_maxColSpan);
+    m_maxColSpanTime = usSince(t0);
+    if (m_lastRc != 0) return false;
+    t0 = chrono::steady_clock::now();
+    m_lastRc = b200spmv_max_alive(m_ctx, m_A->getRows(), nz, &inds[0], &m_maxAlive);  // leaves bits 31 / 30 set
+    m_maxAliveTime = usSince(t0);
+    if (m_lastRc != 0) return false;
+    for (unsigned i = 0; i < nz; i++) inds[i] &= 0x3FFFFFFFu;
+    t0 = chrono::steady_clock::now();
+    m_lastRc = b200spmv_mark_row_starts(m_ctx, m_A->getRows(), nz, &inds[0], 0, 31);
+    m_cmsTime = usSince(t0);
+    return m_lastRc == 0;
+}
+
+bool CudaSpMV::runVectorCacheModel()
+{
+    if (!ok() || m_opt.vcDepth <= 0) return false;
+    int lg = 0;
+    while ((1 << lg) < m_opt.vcDepth) lg++;
+    const unsigned nz = m_A->getNz();
+    const bool cms = m_opt.indexMask != 0xFFFFFFFFu;
+    vector<SpMVIndex> inds(m_A->getInds(), m_A->getInds() + nz);
+    // with cold-miss skip the model reads bit 31 as "first touch of this row" (NoWMVectorCache.scala:240-252).  The
+    // marks are (re)made on the device on this private copy -- the same bits SparseMatrix::markRowStarts sets
+    // (main.cpp:228-229), whether or not the caller's matrix carries them
+    for (unsigned i = 0; i < nz; i++) inds[i] &= 0x3FFFFFFFu;
+    if (cms && (m_lastRc = b200spmv_mark_row_starts(m_ctx, m_A->getRows(), nz, &inds[0], 0, 31)) != 0) return false;
+    m_lastRc = b200spmv_vector_cache_model(m_ctx, nz, &inds[0], lg, cms ? 1 : 0, m_vc);
+    m_vcDone = m_lastRc == 0;
+    return m_vcDone;
+}
+
 uint64_t CudaSpMV::stat64(const std::string &name)
 {
     uint64_t v = 0;
@@ -94,9 +142,19 @@ std::string CudaSpMV::lastError() const { return b200spmv_last_error(m_ctx); }
 std::vector<std::string> CudaSpMV::statKeys()
 {
     // the HardwareSpMV vocabulary (HardwareSpMV.cpp:54-61) first, then SoftwareSpMV's spmvtime, then ours
-    static const char *k[] = {"diffFromGolden", "rows", "cols", "nz", "spmvtime", "xfertime", "setuptime",
-                              "gpus", "slabs", "l2PersistKB", "mode", "cudaError"};
-    return vector<string>(k, k + sizeof(k) / sizeof(k[0]));
+    // ... the preprocessing keys of SoftwareSpMV::statKeys (SoftwareSpMV.cpp:96-108; zero until
+    // measurePreprocessingTimes has run) ...
+    static const char *k[] = {"diffFromGolden", "rows", "cols", "nz", "spmvtime", "cmstime", "maxAliveTime", "maxColSpanTime",
+                              "maxAlive", "maxColSpan", "xfertime", "setuptime", "gpus", "slabs", "l2PersistKB", "mode", "cudaError"};
+    vector<string> keys(k, k + sizeof(k) / sizeof(k[0]));
+    if (m_opt.vcDepth > 0) {
+        // ... and for a "vcmodel" conf the NewCache keys a functional model can know (HardwareSpMVNewCache.cpp:189-204;
+        // the cycle and stall counters of the RTL are not modelled) followed by the model's own counters
+        static const char *v[] = {"readMisses", "ocmDepth", "cms", "reads", "hits", "conflictEvictions", "coldMissSkips",
+                                  "ddrReads", "flushWrites"};
+        keys.insert(keys.end(), v, v + sizeof(v) / sizeof(v[0]));
+    }
+    return keys;
 }
 
 unsigned int CudaSpMV::statInt(std::string name)
@@ -105,7 +163,20 @@ unsigned int CudaSpMV::statInt(std::string name)
     if (name == "rows") return m_A->getRows();
     if (name == "cols") return m_A->getCols();
     if (name == "nz") return m_A->getNz();
-    if (name == "spmvtime") return (unsigned)(stat64("spmvtime_ns") / 1000);   // microseconds, kernels only
+    // microseconds on the compute stream between the first and the last kernel of the step; inside b200spmv_exec that
+    // stream also waits for the slices of x to land, so this includes upload waits (execDeviceOnly: kernels only)
+    if (name == "spmvtime") return (unsigned)(stat64("spmvtime_ns") / 1000);
+    if (name == "cmstime") return m_cmsTime;
+    if (name == "maxAliveTime") return m_maxAliveTime;
+    if (name == "maxColSpanTime") return m_maxColSpanTime;
+    if (name == "maxAlive") return m_maxAlive;
+    if (name == "maxColSpan") return m_maxColSpan;
+    if (m_opt.vcDepth > 0) {
+        static const char *v[] = {"reads", "readMisses", "conflictEvictions", "coldMissSkips", "ddrReads", "flushWrites", "hits"};
+        for (int i = 0; i < 7; i++) if (name == v[i]) return (unsigned)m_vc[i];
+        if (name == "ocmDepth") return (unsigned)m_opt.vcDepth;
+        if (name == "cms") return m_opt.indexMask != 0xFFFFFFFFu ? 1u : 0u;
+    }
     if (name == "xfertime") return (unsigned)(stat64("xfertime_ns") / 1000);
     if (name == "setuptime") return (unsigned)(stat64("setuptime_ns") / 1000);
     if (name == "gpus") return (unsigned)stat64("gpus");

@@ -26,9 +26,11 @@ struct CudaSpMVOptions {
     int slabs;           // column slabs, 0 = auto
     unsigned indexMask;  // 0x3FFFFFFF when the matrix went through SparseMatrix::markRowStarts
     bool requireAligned; // enforce the 64-byte rule of HardwareSpMV.cpp:6-16
+    bool prep;           // conf token "prep": spmvbench calls measurePreprocessingTimes() after exec, like benchmarkSW
+    int vcDepth;         // conf token "vcmodel<depth>": lines of the modelled vector cache (power of two), 0 = no model
     CudaSpMVOptions()
         : device(0), strictOrder(false), persistX(true), accumulate(true), slabs(0), indexMask(0xFFFFFFFFu),
-          requireAligned(false) {}
+          requireAligned(false), prep(false), vcDepth(0) {}
 };
 
 class CudaSpMV : public SpMV {
@@ -42,6 +44,16 @@ public:
     virtual std::vector<std::string> statKeys();
 
     void compareGolden(SpMVData *golden);                 // HardwareSpMV.cpp:37-39: memcmp over rows*8 bytes
+    // SoftwareSpMV::measurePreprocessingTimes (SoftwareSpMV.cpp:72-94) on the device: maxColSpan, maxAlive and the
+    // cold-miss-skip marking of the row-index stream, each timed (microseconds, upload included); fills the
+    // SoftwareSpMV stat keys cmstime, maxAliveTime, maxColSpanTime, maxAlive, maxColSpan.  The matrix is not
+    // modified (the reference marks in place and clears again).
+    bool measurePreprocessingTimes();
+    // The FPGA's direct-mapped vector cache over y, modelled for this matrix (csrc/vcache.cu): fills the NewCache
+    // keys it can know (HardwareSpMVNewCache.cpp:189-204: readMisses, ocmDepth, cms) and the model's own counters.
+    // cms = the matrix was row-start marked (conf token "cms") -> first touches skip the DRAM read.
+    bool runVectorCacheModel();
+    const CudaSpMVOptions &options() const { return m_opt; }
     bool execDeviceOnly(int iters, float *msEach = 0);    // kernels only, x / y already in HBM
     uint64_t stat64(const std::string &name);             // 64-bit statistics (ns timers, nnz > 2^32)
     bool ok() const { return m_ctx != 0 && m_ready; }
@@ -53,6 +65,9 @@ protected:
     bool m_ready, m_allocX, m_allocY;
     int m_golden;  // -1 = not compared, else memcmp result != 0
     int m_lastRc;
+    unsigned m_cmsTime, m_maxAliveTime, m_maxColSpanTime, m_maxAlive, m_maxColSpan;
+    uint64_t m_vc[7];  // reads, readMisses, conflictEvictions, coldMissSkips, ddrReads, flushWrites, hits
+    bool m_vcDone;
 };
 
 #endif

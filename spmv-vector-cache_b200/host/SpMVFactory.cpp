@@ -31,6 +31,13 @@ bool SpMVFactory::parse(const string &conf, CudaSpMVOptions *opt)
         else if (tok == "nopersist") o.persistX = false;
         else if (tok == "overwrite") o.accumulate = false;
         else if (tok == "cms") o.indexMask = 0x3FFFFFFFu;  // matrix went through markRowStarts (main.cpp:228-229)
+        else if (tok == "prep") o.prep = true;             // measurePreprocessingTimes after exec (main.cpp:139)
+        else if (tok.compare(0, 7, "vcmodel") == 0) {      // vcmodel<depth>: model the FPGA's vector cache of that many lines
+            char *end = 0;
+            const long d = strtol(tok.c_str() + 7, &end, 10);
+            if (*end != 0 || d < 1 || d > (1L << 30) || (d & (d - 1)) != 0) return false;
+            o.vcDepth = (int)d;
+        }
         else return false;
         p = q;
     }

@@ -3,6 +3,9 @@
 // "accType" and "matrix" (main.cpp:49-66), golden check inline (main.cpp:222-247).
 //
 //   spmvbench --root <matrices dir> --confs cuda,cuda-strict --matrices circuit204,i64k [--cms 1] [--iters N]
+//   conf tokens: cuda[<device>][-strict][-nopersist][-overwrite][-cms][-prep][-vcmodel<depth>]
+//     -prep            also run SoftwareSpMV::measurePreprocessingTimes' three passes on the GPU (cmstime, maxAlive...)
+//     -vcmodel<depth>  also model the FPGA's vector cache of <depth> lines (NewCache stat keys readMisses, ...)
 //   spmvbench --root <dir>          # no lists: the reference's prompts on stdin (confs ... q, CMS, matrices ... q)
 //
 // Built inside the reference tree (-DB200_USE_REFERENCE_HEADERS) the golden
@@ -131,6 +134,8 @@ int main(int argc, char **argv)
             if (!spmv->exec()) failures++;
             CudaSpMV *cu = dynamic_cast<CudaSpMV *>(spmv);
             if (cu && golden) cu->compareGolden(golden);
+            if (cu && cu->options().prep && !cu->measurePreprocessingTimes()) failures++;  // main.cpp:139 (benchmarkSW)
+            if (cu && cu->options().vcDepth > 0 && !cu->runVectorCacheModel()) failures++;
             printResults(spmv, keys, eff, ms[m]);
             if (cu && iters > 0) {  // device-resident timing, kernels only
                 vector<float> t(iters);

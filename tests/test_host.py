@@ -126,3 +126,42 @@ def test_same_host_code_inside_the_reference_interface():
         assert len(rows) == len(H.FP64_DIRS) and all(r["diffFromGolden"] == "0" for r in rows), out
     rc, out, err = run_bench(REFBENCH, H.MATRICES, "sw", "circuit204")
     assert rc == 0 and "spmvtime" in out
+
+
+@pytest.mark.gpu
+def test_preprocessing_and_vector_cache_vocabularies(built, oracle):
+    """The reference's two other stat vocabularies through the host class and the CLI (missing 4-5):
+    conf token `prep` = SoftwareSpMV::measurePreprocessingTimes (SoftwareSpMV.cpp:72-94) on the device -- maxAlive and
+    maxColSpan must equal the reference's methods (oracle restatement, itself pinned against the compiled reference);
+    `vcmodel<depth>` = the NewCache counters of HardwareSpMVNewCache.cpp:189-204 that a functional model can know,
+    equal to the sequential oracle model for the same depth, with and without cold-miss skip."""
+    names = ["circuit204", "i1k", "row64k"]
+    confs = "cuda-prep-strict,cuda-vcmodel64,cuda-vcmodel1024-cms"
+    rc, out, err = run_bench(os.path.join(built, "spmvbench"), H.MATRICES, confs, ",".join(names))
+    assert rc == 0, err
+    rows = parse_csv(out)
+    assert len(rows) == 3 * len(names)
+    for key in ("cmstime", "maxAliveTime", "maxColSpanTime", "maxAlive", "maxColSpan"):  # SoftwareSpMV.cpp:96-108
+        assert key in rows[0]
+    for r in rows[:len(names)]:
+        m = H.load_matrix_dir(os.path.join(H.MATRICES, r["matrix"]))
+        inds = m.rowind.copy()
+        assert int(r["maxColSpan"]) == oracle.lib.oracle_max_col_span(H.C.c_uint32(m.cols), H.C.c_uint32(m.nnz), H.ptr(m.colptr), H.ptr(inds))
+        assert int(r["maxAlive"]) == oracle.lib.oracle_max_alive(H.C.c_uint32(m.rows), H.C.c_uint32(m.nnz), H.ptr(inds))
+        assert r["diffFromGolden"] == "0"
+    # the vcmodel confs print their own header (keys are built per conf list in the reference too: first run wins),
+    # so re-run them alone to get their columns
+    for conf, depth_log2, cms in (("cuda-vcmodel64", 6, 0), ("cuda-vcmodel1024-cms", 10, 1)):
+        rc, out, err = run_bench(os.path.join(built, "spmvbench"), H.MATRICES, conf, ",".join(names))
+        assert rc == 0, err
+        for r in parse_csv(out):
+            m = H.load_matrix_dir(os.path.join(H.MATRICES, r["matrix"]))
+            inds = m.rowind.copy()
+            if cms:
+                oracle.lib.oracle_mark_row_starts(H.C.c_uint32(m.rows), H.C.c_uint32(m.nnz), H.ptr(inds), H.C.c_int(0), H.C.c_int(31))
+            out7 = np.zeros(7, dtype=np.uint64)
+            oracle.lib.oracle_vector_cache_model(H.C.c_uint32(inds.size), H.ptr(inds), H.C.c_int(depth_log2), H.C.c_int(cms), H.ptr(out7))
+            want = dict(zip(("reads", "readMisses", "conflictEvictions", "coldMissSkips", "ddrReads", "flushWrites", "hits"), (int(v) for v in out7)))
+            assert int(r["ocmDepth"]) == 1 << depth_log2 and int(r["cms"]) == cms
+            for k in ("reads", "readMisses", "conflictEvictions", "coldMissSkips", "ddrReads", "flushWrites", "hits"):
+                assert int(r[k]) == want[k], (conf, r["matrix"], k)

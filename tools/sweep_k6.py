@@ -36,7 +36,7 @@ args = ap.parse_args()
 
 # (name, kind, rows, npr, slabs list)
 WORK = [
-    ("uniform C3", 0, 1 << 24, 32, [3, 4]),
+    ("uniform C3", 0, 1 << 24, 32, [3]),
     ("band16", 3, 1 << 24, 16, [1, 3]),
     ("banded11+5", 2, 1 << 24, 5, [1, 3]),
     ("rmat16M", 1, 1 << 24, 32, [0]),
@@ -49,12 +49,13 @@ if args.only:
 
 VARIANTS = [
     ("k3", {"kernel": 3}),
+    ("k3 nopersist", {"kernel": 3, "_flags": 4}),
+    ("k3 pf0", {"kernel": 3, "prefetch_tiles": 0}),
+    ("k3 pf592", {"kernel": 3, "prefetch_tiles": 592}),
     ("k6 db occ2", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1}),
-    ("k6 nodb occ3", {"kernel": 6, "stream_db": 0, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1}),
     ("k6 nodb occ3 pf1", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1}),
-    ("k6 db occ2 pf2", {"kernel": 6, "stream_db": 1, "stream_pf": 2, "stream_occ": 0, "stream_vchunks": 1}),
-    ("k6 db occ2 nopersist", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1, "_flags": 4}),
-    ("k6 db occ2 dcsr0", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1, "dcsr_x16": 0}),
+    ("k6 nodb occ3 pf1 v8", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 8}),
+    ("k6 nodb pf1 nopersist", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1, "_flags": 4}),
 ]
 if args.ablate:
     VARIANTS = [v for v in VARIANTS if v[0] in ("k6 db occ2", "k6 nodb occ3", "k6 nodb occ3 pf2")]
@@ -78,6 +79,7 @@ for name, kind, rows, npr, slab_list in WORK:
         ref = None
         for vname, opts in VARIANTS:
             e.set_option("dcsr_x16", 96)
+            e.set_option("prefetch_tiles", 148)
             fl = b2.ACCUMULATE | opts.get("_flags", 0)
             for k, v in opts.items():
                 if not k.startswith("_"):
