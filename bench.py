@@ -502,9 +502,9 @@ def main():
     ap.add_argument("--dcsr", type=int, default=None, help="hypersparse-slab threshold x16 (0 = never use spmv_dcsr_kernel)")
     ap.add_argument("--cols", type=int, default=0, help="override the column count (experiments only)")
     ap.add_argument("--slabs", type=int, default=0)
-    ap.add_argument("--kernel", type=int, default=0, help="6 flagged segmented sum by persistent warps (default), 3 one tile per CTA")
-    ap.add_argument("--stream-db", type=int, default=None, help="kernel 6: register double buffer of the entry streams (default 1)")
-    ap.add_argument("--stream-pf", type=int, default=None, help="kernel 6: L2 bulk prefetch distance in warp steps (default 0)")
+    ap.add_argument("--kernel", type=int, default=0, help="3 flagged segmented sum, one tile per CTA (default); 6 the same by persistent warps")
+    ap.add_argument("--stream-db", type=int, default=None, help="kernel 6: register double buffer of the entry streams (default 0)")
+    ap.add_argument("--stream-pf", type=int, default=None, help="kernel 6: L2 bulk prefetch distance in warp steps (default 1)")
     ap.add_argument("--stream-occ", type=int, default=None, help="kernel 6: CTAs per SM")
     ap.add_argument("--stream-vchunks", type=int, default=None, help="kernel 6: chunks per warp")
     ap.add_argument("--no-power", action="store_true", help="banded-power: time plain SpMV steps instead of the power iteration")

@@ -66,8 +66,9 @@ B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx ma
 
 /* Tunables, set before setup: "slabs" (column slabs, 0 = auto), "persist_bytes"
  * (L2 set-aside cap, 0 = device max), "require_aligned" (1 = enforce the 64-byte rule),
- * "keep_csc" (1 = keep the device CSC copy for b200spmv_get_csc), "profile", "kernel" (1..5, see
- * DESIGN.md 3.2; default 3), "ept", "ctas_per_sm" (kernel tuning), "world" then "rank" (take the
+ * "keep_csc" (1 = keep the device CSC copy for b200spmv_get_csc), "profile", "kernel" (3 = flagged
+ * segmented sum with one tile per CTA, the default; 6 = the same by persistent warps, with its tuning knobs
+ * "stream_db", "stream_pf", "stream_occ", "stream_vchunks"), "world" then "rank" (take the
  * place of rank r of w in the nnz-balanced row-block split WITHOUT a communicator: a single SpMV
  * needs no collective; b200spmv_power_iterate does and refuses).
  * Kernel selection per slab: "dcsr_x16" (thread-per-row kernel when a slab holds fewer than value/16 entries

@@ -215,6 +215,13 @@ def row_splits(rowptr, world):
     return out
 
 
+def exec_x_blocks(cols, world):
+    """Host statement of csrc/multi.cu b2_exec_x_block: the columns of x rank r uploads in b200spmv_exec when a
+    communicator is attached ([lo_r, hi_r), boundaries cut to whole 32-byte units); the rest arrives over NVLink."""
+    lo = [(cols * r // world) & ~3 for r in range(world)]
+    return [(lo[r], cols if r + 1 == world else lo[r + 1]) for r in range(world)]
+
+
 def comm_unique_id():
     buf = C.create_string_buffer(128)
     rc = lib().b200spmv_comm_unique_id(buf)

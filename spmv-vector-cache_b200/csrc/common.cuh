@@ -50,9 +50,9 @@ struct b200spmv_ctx {
     int64_t opt_persist_bytes = 0;  // 0 = device max
     int opt_require_aligned = 0;
     int opt_keep_csc = 0;
-    int opt_kernel = 6;           // 3 = flagged segmented sum, one tile per CTA; 6 = the same by persistent warps (spmv.cu)
-    int opt_stream_db = 1;        // kernel 6: register double buffer for the entry streams
-    int opt_stream_pf = 0;        // kernel 6: L2 bulk prefetch (UBLKPF) distance in warp steps (0 = off)
+    int opt_kernel = 3;           // 3 = flagged segmented sum, one tile per CTA (default); 6 = the same by persistent warps (spmv.cu)
+    int opt_stream_db = 0;        // kernel 6: register double buffer for the entry streams
+    int opt_stream_pf = 1;        // kernel 6: L2 bulk prefetch (UBLKPF) distance in warp steps (0 = off)
     int opt_stream_occ = 0;       // kernel 6: CTAs per SM (0 = what the launch bounds allow: 2 with the double buffer, else 3)
     int opt_stream_vchunks = 1;   // kernel 6: chunks per warp (1 = one contiguous chunk per warp)
     int opt_dcsr_x16 = 96;        // slabs with < this/16 (= 6) entries per non-empty row use spmv_dcsr_kernel (0 = never)

@@ -29,20 +29,19 @@ def b2():
 # sees every matrix; 96: the shipped threshold (< 6 entries per non-empty row); 1 << 20: every slab goes to
 # spmv_dcsr_kernel
 ENGINES = {
-    "stream": (6, {}, 0),                                             # kernel 6 as shipped (register double buffer)
-    "stream-nodb": (6, {"stream_db": 0}, 0),                          # ... single buffer
-    "stream-pf": (6, {"stream_db": 0, "stream_pf": 2}, 0),            # ... with the L2 bulk prefetch
-    "stream-v3": (6, {"stream_vchunks": 3, "stream_occ": 1}, 0),      # ... several chunks per warp
-    "flag": (3, {}, 0),                                               # kernel 3 (CTA tiles)
-    "default": (6, {}, 96),
-    "dcsr-always": (6, {}, 1 << 20),
+    "flag": (3, {}, 0),                                               # kernel 3 (CTA tiles), the default
+    "stream": (6, {}, 0),                                             # kernel 6 as shipped (single buffer + L2 prefetch)
+    "stream-db": (6, {"stream_db": 1, "stream_pf": 0}, 0),            # ... register double buffer
+    "stream-v3": (6, {"stream_vchunks": 3, "stream_occ": 1, "stream_pf": 2}, 0),  # ... several chunks per warp
+    "default": (3, {}, 96),
+    "dcsr-always": (3, {}, 1 << 20),
 }
 
 
 @pytest.fixture(params=list(ENGINES), ids=list(ENGINES))
 def eng(b2, request):
-    """every throughput kernel configuration: 6 = flagged segmented sum by persistent warps (default),
-    3 = the same with one tile per CTA"""
+    """every throughput kernel configuration: 3 = flagged segmented sum, one tile per CTA (default),
+    6 = the same by persistent warps"""
     kernel, opts, dcsr = ENGINES[request.param]
     e = b2.Engine(0)
     e.set_option("kernel", kernel)

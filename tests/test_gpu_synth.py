@@ -61,13 +61,14 @@ def test_synthetic_small_vs_oracle(b2, oracle, kind, rows, npr, dtype, slabs):
     e.close()
 
 
-@pytest.mark.parametrize("dtype", ["u64", "f64"])
-def test_headline_config_full_size_properties(b2, oracle, dtype):
+@pytest.mark.parametrize("dtype,kernel", [("u64", 3), ("f64", 3), ("u64", 6)])
+def test_headline_config_full_size_properties(b2, oracle, dtype, kernel):
     """configs[2]: uniform 16M x 16M, 32 nnz/row.  Too large for the host oracle, so:
     rows regenerated on the host from the counter-based definition (spot check, exact for
     u64 / strict fp64), merge-path == strict kernel (u64 bit-exact), and linearity."""
     rows, npr = 1 << 24, 32
     e = b2.Engine(0)
+    e.set_option("kernel", kernel)
     e.setup_synthetic(0, rows, rows, npr, SEED, DT(b2, dtype))
     assert e.stat("nz") == rows * npr
     e.fill_x_synthetic(SEED + 1)

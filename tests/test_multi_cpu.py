@@ -101,3 +101,49 @@ def test_reference_arm_nonzero_rank_is_silent():
     p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
                         "--steps", "1", "--warmup", "0"], env=env, capture_output=True, text=True, timeout=120)
     assert p.returncode == 0 and p.stdout.strip() == ""
+
+
+def _gather_worker(rank, world, port, cols, q):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(ROOT, "spmv-vector-cache_b200"))
+    import b200spmv as b2
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    host_x = np.arange(cols, dtype=np.float64) * 0.5 + 1.0       # the same host vector on every rank
+    dev_x = np.full(cols, np.nan)                                  # this rank's device copy: nothing uploaded yet
+    blocks = b2.exec_x_blocks(cols, world)
+    lo, hi = blocks[rank]
+    dev_x[lo:hi] = host_x[lo:hi]                                   # the only host->device copy of x on this rank
+    for r, (a, b) in enumerate(blocks):                            # grouped broadcasts = variable-size all-gather
+        t = torch.from_numpy(dev_x[a:b].copy())
+        dist.broadcast(t, r)
+        dev_x[a:b] = t.numpy()
+    q.put((rank, hi - lo, bool(np.array_equal(dev_x, host_x))))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("cols", [1 << 16, (1 << 16) + 1234, 37])
+def test_exec_x_upload_split_world2_gloo(cols):
+    """b200spmv_exec over several ranks (csrc/api.cu, multi.cu b2_exec_gather_x): every rank uploads only its block of
+    the host x and the blocks are exchanged -- here the same schedule over gloo with world_size 2.  The blocks tile
+    [0, cols) exactly, their boundaries are whole 32-byte units, every rank ends with the full x, and no rank moved
+    more than its share (+ 3 elements of rounding) over its host link."""
+    import torch.multiprocessing as mp
+    sys.path.insert(0, os.path.join(ROOT, "spmv-vector-cache_b200"))
+    import b200spmv as b2
+    for world in (2, 3, 8):
+        bl = b2.exec_x_blocks(cols, world)
+        assert bl[0][0] == 0 and bl[-1][1] == cols and all(bl[r][1] == bl[r + 1][0] for r in range(world - 1))
+        assert all(lo % 4 == 0 for lo, _ in bl)
+        assert max(hi - lo for lo, hi in bl) <= cols // world + 4 + (cols % world > 0) + 3
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29900 + (os.getpid() % 90)
+    ps = [ctx.Process(target=_gather_worker, args=(r, 2, port, cols, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    got = sorted(q.get(timeout=120) for _ in range(2))
+    for p in ps:
+        p.join(60)
+    assert all(ok for _, _, ok in got)
+    assert sum(n for _, n, _ in got) == cols

@@ -80,8 +80,10 @@ __global__ void __launch_bounds__(256) port_kernel(const uint32_t *__restrict__ 
         if (GATHER) {
 #pragma unroll
             for (int k = 0; k < 8; k++) {
-                rng = rng * 1664525u + 1013904223u;
-                g[k] = __ldg(reinterpret_cast<const unsigned long long *>(tab + ((rng >> 7) & tab_mask)));
+                rng += 0x9E3779B9u;  // counter; murmur3 finaliser below: lanes must not stride regularly (L2 slice camping)
+                uint32_t h = rng;
+                h ^= h >> 16; h *= 0x85EBCA6Bu; h ^= h >> 13; h *= 0xC2B2AE35u; h ^= h >> 16;
+                g[k] = __ldg(reinterpret_cast<const unsigned long long *>(tab + (h & tab_mask)));
             }
         }
         if (TMA) {
@@ -145,7 +147,7 @@ int main()
     CK(cudaMalloc(&out, 64));
     CK(cudaMemset(idx, 1, n * 4));
     CK(cudaMemset(val, 1, n * 8));
-    for (int mb : {8, 32, 48}) {
+    for (int mb : {32, 64}) {
         const uint32_t entries = (uint32_t)mb * 1048576u / 8u;
         uint32_t mask = 1;
         while (mask * 2 <= entries) mask *= 2;

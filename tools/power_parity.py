@@ -68,6 +68,29 @@ def main():
                       (rank, name, rows, slabs, e.stat("slabs"), exchange, "ok" if ok else "MISMATCH", err), flush=True)
                 bad += not ok
                 del e
+    # b200spmv_exec over several ranks: each rank uploads 1/world of the host x and the rest arrives over NVLink
+    # (collective call); every rank's block of y must equal the single-GPU result bit for bit (u64), with the
+    # gather on and off, overwrite and accumulate
+    for rows in ((1 << 20) + 8 * 977, 1 << 21):
+        single = make(local, 0, 1, b2.U64, rows, 5, 3, False)
+        rng = np.random.default_rng(99)
+        x = rng.integers(0, 1 << 63, rows, dtype=np.uint64)
+        y0 = rng.integers(0, 1 << 63, rows, dtype=np.uint64)
+        want = {fl: single.exec(x, y0.copy(), fl) for fl in (0, b2.ACCUMULATE)}
+        del single
+        for gather in (1, 0):
+            e = make(local, rank, world, b2.U64, rows, 5, 3, False)
+            e.set_option("exec_gather", gather)
+            rb, re = e.stat("row_begin"), e.stat("row_end")
+            for fl in (0, b2.ACCUMULATE, 0):
+                e.set_x(np.zeros(rows, dtype=np.uint64))
+                y = e.exec(x, y0.copy(), fl)
+                ok = np.array_equal(y[rb:re], want[fl][rb:re])
+                print("rank %d exec rows %d gather %d flags %d h2d %d: %s" % (rank, rows, gather, fl, e.stat("exec_h2d_bytes"), "ok" if ok else "MISMATCH"), flush=True)
+                bad += not ok
+            if gather:
+                bad += not (e.stat("exec_h2d_bytes") <= 8 * (rows // world + 8) + 0)  # overwrite: 1/world of x only
+            del e
     t = torch.tensor([bad], device="cuda")
     dist.all_reduce(t)
     if rank == 0:
