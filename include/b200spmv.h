@@ -71,9 +71,10 @@ B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx ma
  * "stream_db", "stream_pf", "stream_occ", "stream_vchunks"), "world" then "rank" (take the
  * place of rank r of w in the nnz-balanced row-block split WITHOUT a communicator: a single SpMV
  * needs no collective; b200spmv_power_iterate does and refuses).
- * Kernel selection per slab: "dcsr_x16" (thread-per-row kernel when a slab holds fewer than value/16 entries
- * per non-empty row, default 96; 0 = never) and "dcsr_maxrow" (... and no row piece longer than this, default
- * 64); "prefetch_tiles" (kernel 3: L2 bulk prefetch distance in CTAs, default 148), "prefetch_x" (1 = stream a
+ * Kernel selection per slab: "dcsr_x16" (which slabs run the thread-per-row kernel: -1, the default = whichever
+ * kernel was faster when setup timed both on the slab; 0 = never; n > 0 = slabs with fewer than n/16 entries per
+ * non-empty row) and "dcsr_maxrow" (... and only slabs with no row piece longer than this, default 64; stats
+ * "slab_dcsr_<i>", "tunetime_ns"); "prefetch_tiles" (kernel 3: L2 bulk prefetch distance in CTAs, default 148), "prefetch_x" (1 = stream a
  * slab's slice of x into L2 before its kernel; measured useless, default 0), "graph" (b200spmv_exec_device
  * replays a CUDA graph of one step, default 1).
  * "pin_host" (1 = b200spmv_exec page-locks the caller's pageable x / y in place with cudaHostRegister the first

@@ -103,7 +103,7 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "stream_pf") { if (value < 0 || value > 64) return b2_fail(ctx, B200SPMV_EINVAL, "stream_pf must be 0..64"); ctx->opt_stream_pf = (int)value; }
     else if (k == "stream_occ") { if (value < 0 || value > 8) return b2_fail(ctx, B200SPMV_EINVAL, "stream_occ must be 0..8"); ctx->opt_stream_occ = (int)value; }
     else if (k == "stream_vchunks") { if (value < 1 || value > 64) return b2_fail(ctx, B200SPMV_EINVAL, "stream_vchunks must be 1..64"); ctx->opt_stream_vchunks = (int)value; }
-    else if (k == "dcsr_x16") ctx->opt_dcsr_x16 = (int)value;
+    else if (k == "dcsr_x16") { if (value < -1 || value > (1 << 20)) return b2_fail(ctx, B200SPMV_EINVAL, "dcsr_x16 must be -1 (measured), 0 (never) or a threshold in 1/16 entries per row"); ctx->opt_dcsr_x16 = (int)value; }
     else if (k == "prefetch_tiles") ctx->opt_prefetch_tiles = (int)std::max<int64_t>(0, value);
     else if (k == "graph") ctx->opt_graph = (int)value;
     else if (k == "prefetch_x") ctx->opt_prefetch_x = (int)value;
@@ -142,7 +142,7 @@ static int choose_slabs(const b200spmv_ctx *ctx)
     // let part of the gathers go to HBM (profiles/r01_c5_shard_sweep.txt, r01_c4_shard_sweep.txt).
     // (per NON-EMPTY row: the empty rows of a skewed block cost the kernels nothing; profiles/r01_c4_shard_sweep.txt)
     const double per_row = ctx->nonempty_rows ? (double)ctx->local_nnz / (double)ctx->nonempty_rows : 0.0;
-    int by_rows = (int)(per_row / 8.0);
+    int by_rows = (int)(per_row / 8.0 + 0.5);  // banded(11)+5 has 15.99 per row (short rows at the edges): 2 slabs, 245 vs 210 GNNZ/s
     // Column skew (R-MAT: 3/4 of the entries sit in the lower half of the columns): most of the uniform slabs
     // then hold far fewer entries per row than the average says, so fewer of them pay off.
     if (ctx->upper_half_nnz * 100 < ctx->local_nnz * 35) by_rows = (by_rows * 2 + 2) / 3;
@@ -233,6 +233,7 @@ static int csc_to_csr(b200spmv_ctx *ctx, uint32_t index_mask)
     B2_CHECK(ctx, cudaMemsetAsync(ctx->d_y, 0, (size_t)ctx->rows * 8, s));
     B2_CHECK(ctx, cudaStreamSynchronize(s));
     ctx->persist_set = false;
+    B2_TRY(b2_tune_slab_kernels(ctx));
     ctx->ready = true;
     return 0;
 }
@@ -604,6 +605,12 @@ extern "C" int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *o
     else if (k == "exchange_mode") *out = (uint64_t)ctx->exchange_mode;
     else if (k == "exec_h2d_bytes") *out = ctx->exec_h2d_bytes;
     else if (k == "exec_d2h_bytes") *out = ctx->exec_d2h_bytes;
+    else if (k.rfind("slab_dcsr_", 0) == 0) {
+        const int i = atoi(k.c_str() + 10);
+        if (i < 0 || i >= ctx->slabs) return b2_fail(ctx, B200SPMV_EINVAL, "no such slab");
+        *out = (uint64_t)(ctx->h_slab_dcsr[i] == 1);
+    }
+    else if (k == "tunetime_ns") *out = ctx->tunetime_ns;
     else if (k.rfind("slab_ns_", 0) == 0 || k.rfind("slab_nnz_", 0) == 0 || k.rfind("slab_rows_", 0) == 0 || k.rfind("slab_maxrow_", 0) == 0) {
         const int i = atoi(k.c_str() + k.rfind('_') + 1);
         if (i < 0 || i >= ctx->slabs) return b2_fail(ctx, B200SPMV_EINVAL, "no such slab");

@@ -55,7 +55,8 @@ struct b200spmv_ctx {
     int opt_stream_pf = 1;        // kernel 6: L2 bulk prefetch (UBLKPF) distance in warp steps (0 = off)
     int opt_stream_occ = 0;       // kernel 6: CTAs per SM (0 = what the launch bounds allow: 2 with the double buffer, else 3)
     int opt_stream_vchunks = 1;   // kernel 6: chunks per warp (1 = one contiguous chunk per warp)
-    int opt_dcsr_x16 = 96;        // slabs with < this/16 (= 6) entries per non-empty row use spmv_dcsr_kernel (0 = never)
+    int opt_dcsr_x16 = -1;        // which slabs run spmv_dcsr_kernel: -1 = measured per slab at setup (b2_tune_slab_kernels),
+                                  // 0 = never, n > 0 = those with < n/16 entries per non-empty row
     int opt_prefetch_tiles = 148; // kernel 3: L2 bulk prefetch (UBLKPF) of the tile this many CTAs ahead (0 = off)
     int opt_own_slabs = 0;        // 1: align the slabs with the ranks' blocks of x (set before setup; see own_lo)
     int opt_exchange = 2;         // with own_slabs: 1 = NCCL all-gather under the own-block slabs, 2 = peer pulls
@@ -101,6 +102,10 @@ struct b200spmv_ctx {
     uint32_t h_slab_nnz[64] = {0};
     uint32_t h_nseg[64] = {0};         // non-empty rows per slab
     uint32_t h_maxrow[64] = {0};       // longest row piece per slab
+    int8_t h_slab_dcsr[64] = {0};      // measured choice per slab (opt_dcsr_x16 < 0): 1 = thread-per-row kernel
+    uint64_t tune_mask = 0;            // b2_tune_slab_kernels: the slabs being measured ...
+    int tune_force = 0;                // ... 1 = with the flagged kernel, 2 = with the thread-per-row kernel
+    uint64_t tunetime_ns = 0;
     bool flagged = false;              // colind carries row-start flags in bit 31
     uint32_t colmask = 0xFFFFFFFFu;    // mask that strips the flag
     uint64_t padded_nnz = 0;
@@ -225,6 +230,7 @@ int b2_count_nonempty(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint3
 int b2_build_flags(b200spmv_ctx *ctx);
 constexpr uint32_t B2_FLAG_TILE = 2048;  // entries per CTA of kernel 3 (8 warp steps of kernel 6); slabs are padded to it
 int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s);
+int b2_tune_slab_kernels(b200spmv_ctx *ctx);
 int b2_spmv_prepare(b200spmv_ctx *ctx, int flags, cudaStream_t s);
 bool b2_last_slab_chunkable(const b200spmv_ctx *ctx, int flags);
 void b2_profile_collect(b200spmv_ctx *ctx);

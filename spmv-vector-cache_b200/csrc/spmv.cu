@@ -25,6 +25,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include <chrono>
 
 namespace {
 
@@ -684,11 +685,19 @@ int b2_build_flags(b200spmv_ctx *ctx)
     return 0;
 }
 
+// Does this slab run the thread-per-row kernel?  Only slabs without a long row piece qualify (dcsr_maxrow).  By
+// default the answer was measured at setup (b2_tune_slab_kernels); option dcsr_x16 >= 0 replaces the measurement
+// by a fixed rule (0 = never, n = fewer than n/16 entries per non-empty row).
+static bool dcsr_candidate(const b200spmv_ctx *ctx, int sl)
+{
+    return ctx->h_nseg[sl] > 0 && ctx->h_maxrow[sl] <= (uint32_t)ctx->opt_dcsr_maxrow;
+}
 static bool dcsr_slab(const b200spmv_ctx *ctx, int sl)
 {
-    const uint32_t nseg = ctx->h_nseg[sl];
-    return ctx->opt_dcsr_x16 > 0 && nseg > 0 && (uint64_t)ctx->h_slab_nnz[sl] * 16 < (uint64_t)nseg * ctx->opt_dcsr_x16 &&
-           ctx->h_maxrow[sl] <= (uint32_t)ctx->opt_dcsr_maxrow;
+    if (ctx->tune_force) return ctx->tune_force == 2 && (ctx->tune_mask >> sl & 1);
+    if (!dcsr_candidate(ctx, sl)) return false;
+    if (ctx->opt_dcsr_x16 < 0) return ctx->h_slab_dcsr[sl] == 1;
+    return ctx->opt_dcsr_x16 > 0 && (uint64_t)ctx->h_slab_nnz[sl] * 16 < (uint64_t)ctx->h_nseg[sl] * ctx->opt_dcsr_x16;
 }
 // Will b2_spmv_launch cut the last slab's kernel into row chunks (and record ev_rowchunk[])?  The flagged layout
 // only: the tiles of kernel 3 are consecutive pieces of the entry stream, hence of the rows (whichever of kernels
@@ -889,6 +898,64 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
         B2_CHECK(ctx, cudaGetLastError());
     }
     ctx->last_mode = strict ? 0 : ctx->opt_kernel;
+    return 0;
+}
+
+// Flagged kernel or thread-per-row kernel?  Which one is faster on a slab of short rows depends on more than the
+// mean row length: uniform 4 per row favours the thread-per-row kernel by 8 %, the three slabs of banded(11)+5
+// (5.85 per non-empty row, but a mixture of 12.7 inside the diagonal block and 1.7 outside) favour the flagged kernel by
+// 50 %, and with 8 slabs of the same matrix it is the other way round by 43 % (profiles/r02_sweep_dcsr.txt).  So
+// when some slab qualifies (no long row piece, fewer than 8 entries per non-empty row, big enough to time), setup ends
+// with whole steps y += A*x timed slab by slab (the per-launch events of option "profile"): three with the flagged
+// kernel everywhere, three with the thread-per-row kernel on the qualifying slabs, the first of each untimed.  Whole
+// steps, because a slab run on its own over and over finds its slice of x already in L2, which it never does in
+// use.  The thread-per-row kernel is kept where it wins by more than 5 % (a tie must not flip between two setups of
+// the same matrix).  x and y are zero at this point; y is zeroed again afterwards (inf times 0 would leave a NaN).
+int b2_tune_slab_kernels(b200spmv_ctx *ctx)
+{
+    memset(ctx->h_slab_dcsr, 0, sizeof ctx->h_slab_dcsr);
+    ctx->tunetime_ns = 0;
+    ctx->tune_mask = 0;
+    if (!ctx->flagged || ctx->local_rows == 0) return 0;
+    for (int sl = 0; sl < ctx->slabs; sl++) {
+        const uint64_t nnz = ctx->h_slab_nnz[sl], nseg = ctx->h_nseg[sl];
+        if (!dcsr_candidate(ctx, sl) || nnz >= 8 * nseg) continue;
+        if (nnz < (1u << 18)) ctx->h_slab_dcsr[sl] = nnz < 6 * nseg;  // launch-latency sized: the fixed rule of round 1
+        else ctx->tune_mask |= 1ull << sl;
+    }
+    if (!ctx->tune_mask || ctx->opt_dcsr_x16 >= 0) return 0;  // nothing to measure / a fixed rule was asked for
+    cudaStream_t s = ctx->stream;
+    const auto t_begin = std::chrono::steady_clock::now();
+    const int profile_was = ctx->opt_profile;
+    uint64_t best[3][64];
+    memset(best, 0xFF, sizeof best);
+    int rc = 0;
+    for (int which = 1; which <= 2 && !rc; which++) {
+        ctx->tune_force = which;
+        for (int rep = 0; rep < 3 && !rc; rep++) {
+            ctx->opt_profile = rep > 0;
+            ctx->prof_n = 0;
+            memset(ctx->prof_slab_ns, 0, sizeof ctx->prof_slab_ns);
+            rc = b2_spmv_launch(ctx, B200SPMV_ACCUMULATE, s);
+            if (!rc && cudaStreamSynchronize(s) != cudaSuccess) rc = b2_fail(ctx, B200SPMV_ECUDA, "slab kernel measurement failed");
+            if (rc || rep == 0) continue;
+            b2_profile_collect(ctx);
+            for (int sl = 0; sl < ctx->slabs; sl++) best[which][sl] = std::min(best[which][sl], ctx->prof_slab_ns[sl]);
+        }
+    }
+    ctx->tune_force = 0;
+    ctx->opt_profile = profile_was;
+    ctx->prof_n = 0;
+    ctx->merge_kernel_ns = 0;
+    ctx->merge_kernel_launches = 0;
+    memset(ctx->prof_slab_ns, 0, sizeof ctx->prof_slab_ns);
+    if (rc) return rc;
+    for (int sl = 0; sl < ctx->slabs; sl++)
+        if (ctx->tune_mask >> sl & 1) ctx->h_slab_dcsr[sl] = (double)best[2][sl] < 0.95 * (double)best[1][sl];
+    B2_CHECK(ctx, cudaMemsetAsync(ctx->d_y, 0, (size_t)ctx->rows * 8, s));
+    B2_CHECK(ctx, cudaStreamSynchronize(s));
+    ctx->launches = 0;
+    ctx->tunetime_ns = (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t_begin).count();
     return 0;
 }
 

@@ -26,14 +26,15 @@ def b2():
 
 
 # (kernel, options, dcsr_x16).  dcsr_x16 0: never hand a slab to the thread-per-row kernel, so the kernel under test
-# sees every matrix; 96: the shipped threshold (< 6 entries per non-empty row); 1 << 20: every slab goes to
-# spmv_dcsr_kernel
+# sees every matrix; -1: as shipped (measured per slab at setup; slabs too small to time use < 6 entries per non-empty
+# row); 96: that rule for every slab; 1 << 20: every slab goes to spmv_dcsr_kernel
 ENGINES = {
     "flag": (3, {}, 0),                                               # kernel 3 (CTA tiles), the default
     "stream": (6, {}, 0),                                             # kernel 6 as shipped (single buffer + L2 prefetch)
     "stream-db": (6, {"stream_db": 1, "stream_pf": 0}, 0),            # ... register double buffer
     "stream-v3": (6, {"stream_vchunks": 3, "stream_occ": 1, "stream_pf": 2}, 0),  # ... several chunks per warp
-    "default": (3, {}, 96),
+    "default": (3, {}, -1),
+    "dcsr-short": (3, {}, 96),
     "dcsr-always": (3, {}, 1 << 20),
 }
 

@@ -38,7 +38,7 @@ args = ap.parse_args()
 WORK = [
     ("uniform C3", 0, 1 << 24, 32, [3]),
     ("band16", 3, 1 << 24, 16, [1, 3]),
-    ("banded11+5", 2, 1 << 24, 5, [1, 3]),
+    ("banded11+5", 2, 1 << 24, 5, [1, 2, 3]),
     ("rmat16M", 1, 1 << 24, 32, [0]),
     ("uniform 4M (x in L2)", 0, 1 << 22, 32, [1]),
 ]
@@ -56,6 +56,10 @@ VARIANTS = [
     ("k6 nodb occ3 pf1", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1}),
     ("k6 nodb occ3 pf1 v8", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 8}),
     ("k6 nodb pf1 nopersist", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1, "_flags": 4}),
+    ("k3 never dcsr", {"kernel": 3, "dcsr_x16": 0}),
+    ("k3 never dcsr nopersist", {"kernel": 3, "dcsr_x16": 0, "_flags": 4}),
+    ("k6 never dcsr", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1, "dcsr_x16": 0}),
+    ("k6 never dcsr nopersist", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1, "dcsr_x16": 0, "_flags": 4}),
 ]
 if args.ablate:
     VARIANTS = [v for v in VARIANTS if v[0] in ("k6 db occ2", "k6 nodb occ3", "k6 nodb occ3 pf2")]
@@ -78,7 +82,7 @@ for name, kind, rows, npr, slab_list in WORK:
             flush=True)
         ref = None
         for vname, opts in VARIANTS:
-            e.set_option("dcsr_x16", 96)
+            e.set_option("dcsr_x16", -1)
             e.set_option("prefetch_tiles", 148)
             fl = b2.ACCUMULATE | opts.get("_flags", 0)
             for k, v in opts.items():
