@@ -258,10 +258,10 @@ class Job:
             eng.set_option("own_slabs", 1)
         if args.prefetch_x is not None:
             eng.set_option("prefetch_x", args.prefetch_x)
-        if exchange in ("pull", "overlap") and self.world > 1 and shard and not args.shard:
+        if exchange in ("pull", "overlap", "packed") and self.world > 1 and shard and not args.shard:
             # slabs aligned with the ranks' x blocks: the exchange of the other blocks runs under the own-block slabs
-            eng.set_option("own_slabs", 1)
-            eng.set_option("exchange", 2 if exchange == "pull" else 1)
+            eng.set_option("own_slabs", args.own_layout)
+            eng.set_option("exchange", {"pull": 2, "overlap": 1, "packed": 3}[exchange])
             if args.pull_streams:
                 eng.set_option("pull_streams", args.pull_streams)
         return eng
@@ -345,7 +345,8 @@ class Job:
         if power and self.world > 1:
             out["x_exchange_ms_last_step"] = eng.stat("xchgtime_ns") * 1e-6
             out["exchange"] = ["NCCL all-gather after the step", "NCCL all-gather under the own-block slabs",
-                               "peer pulls block by block under the slabs"][eng.stat("exchange_mode")]
+                               "peer pulls block by block under the slabs",
+                               "peer pulls of PACKED blocks (only the columns the puller gathers) under the slabs"][eng.stat("exchange_mode")]
         # the dominant kernel alone (roofline), same workload, events around each launch
         eng.set_option("profile", 1)
         psteps = min(steps, 20)
@@ -432,7 +433,7 @@ def run_ours(args):
     if args.workload == "uniform" and not args.no_others and not args.shard:
         others = {}
         specs = [("rmat", "rmat", 20, None)]
-        for ex in (("nccl", "pull") if world > 1 else ("pull",)):
+        for ex in (("nccl", "pull", "packed") if world > 1 else ("pull",)):
             specs.append(("banded_power" + ("_" + ex if world > 1 else ""), "banded-power", 100, ex))
         for key, wl, k_steps, ex in specs:
             try:
@@ -512,9 +513,12 @@ def main():
     ap.add_argument("--graph", type=int, default=None, help="0: do not replay a CUDA graph in exec_device")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
     ap.add_argument("--no-persist", action="store_true")
-    ap.add_argument("--exchange", choices=["pull", "overlap", "nccl"], default="pull",
+    ap.add_argument("--exchange", choices=["pull", "overlap", "nccl", "packed"], default="pull",
                     help="power iteration over several GPUs: how the replicated x is refreshed (DESIGN.md section 7)")
     ap.add_argument("--pull-streams", type=int, default=0)
+    ap.add_argument("--own-layout", type=int, default=1, choices=[1, 2],
+                    help="power iteration over several GPUs: 1 = every rank's block of x is its own slab(s); 2 = own block + one slab for "
+                         "all blocks left of it + one for all blocks right of it (fewer passes over y)")
     ap.add_argument("--prefetch-x", type=int, default=None, help="1: bulk-prefetch each slab's x slice into L2 before its kernel")
     ap.add_argument("--own-slabs", action="store_true", help="with --shard: cut the slabs along the ranks' x blocks")
     ap.add_argument("--per-slab", action="store_true", help="add the kernel time of every slab to config")

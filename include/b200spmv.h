@@ -82,11 +82,15 @@ B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx ma
  * destroyed -- for callers whose vectors outlive the context's use of them, as SpMV objects' do; default 0).
  * For iterated SpMV over several ranks: "own_slabs" (1 = cut the column slabs along the ranks' blocks of
  * x, so that b200spmv_power_iterate can run the slabs of a rank's own block while the other blocks are
- * still on the wire), "exchange" (with own_slabs: 2 = the other blocks are pulled from the peers' x over
- * NVLink by the copy engines through CUDA IPC mappings, block by block, each block's slabs starting when
- * it has landed -- the default, falls back to 1 where peers cannot be mapped; 1 = one NCCL all-gather under
- * the own-block slabs), "pull_streams" (copy streams of exchange 2, default 1).  Stat "exchange_mode"
- * reports what the last b200spmv_power_iterate did (0 = NCCL all-gather after the step). */
+ * still on the wire; 2 = the same for the own block, but ONE slab for all the blocks left of it and one for
+ * all the blocks right of it: fewer passes over y), "exchange" (with own_slabs: 2 = the other blocks are pulled
+ * from the peers' x over NVLink by the copy engines through CUDA IPC mappings, block by block, each slab starting
+ * when the last of its blocks has landed -- the default, falls back to 1 where peers cannot be mapped; 3 = the same
+ * with PACKED blocks: the owner packs, per peer, only the columns that peer's rows gather, the peer pulls the packed
+ * block and its remote slabs index it through a renumbered copy of the column indices; x is whole again when
+ * b200spmv_power_iterate returns; 1 = one NCCL all-gather under the own-block slabs), "pull_streams" (copy streams of
+ * exchanges 2 and 3, default 1).  Stat "exchange_mode" reports what the last b200spmv_power_iterate did (0 = NCCL
+ * all-gather after the step). */
 B200SPMV_API int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t value);
 
 /* ---- setup: upload CSC, transpose to CSR on the device (once, amortised) ------------- */

@@ -25,6 +25,7 @@ static void release_matrix(b200spmv_ctx *ctx)
     b2_free(ctx->csc_colptr); b2_free(ctx->csc_rowind);
     { uint64_t *v = (uint64_t *)ctx->csc_vals; b2_free(v); ctx->csc_vals = nullptr; }
     b2_close_peers(ctx);
+    b2_close_packed(ctx);
     { uint64_t *v = (uint64_t *)ctx->d_x; b2_free(v); ctx->d_x = nullptr; }
     { uint64_t *v = (uint64_t *)ctx->d_y; b2_free(v); ctx->d_y = nullptr; }
     { uint64_t *v = (uint64_t *)ctx->d_yin; b2_free(v); ctx->d_yin = nullptr; }
@@ -109,11 +110,12 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     else if (k == "prefetch_x") ctx->opt_prefetch_x = (int)value;
     else if (k == "pin_host") ctx->opt_pin_host = value != 0;
     else if (k == "dcsr_maxrow") ctx->opt_dcsr_maxrow = (int)value;
-    else if (k == "exchange") { if (value < 1 || value > 2) return b2_fail(ctx, B200SPMV_EINVAL, "exchange must be 1 or 2"); ctx->opt_exchange = (int)value; }
+    else if (k == "exchange") { if (value < 1 || value > 3) return b2_fail(ctx, B200SPMV_EINVAL, "exchange must be 1, 2 or 3"); ctx->opt_exchange = (int)value; }
     else if (k == "pull_streams") { if (value < 1 || value > 4) return b2_fail(ctx, B200SPMV_EINVAL, "pull_streams must be 1..4"); ctx->opt_pull_streams = (int)value; }
     else if (k == "own_slabs") {
         if (ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "set own_slabs before setup");
-        ctx->opt_own_slabs = value != 0;
+        if (value < 0 || value > 2) return b2_fail(ctx, B200SPMV_EINVAL, "own_slabs must be 0, 1 or 2");
+        ctx->opt_own_slabs = (int)value;
     }
     else if (k == "world" || k == "rank") {
         // row-block sharding without a communicator: a single SpMV needs no collective, so a
@@ -172,11 +174,30 @@ static int csc_to_csr(b200spmv_ctx *ctx, uint32_t index_mask)
         // the slabs of this rank's own block can run while the other blocks are still on the wire
         const int per_block = (int)b2_div_up((uint64_t)ctx->slabs, (uint64_t)ctx->world);
         if (per_block * ctx->world > 64) own = false;
-        else {
+        else if (ctx->opt_own_slabs == 2) {
+            // ... or only the own block is, and all the blocks left of it form one slab and all the blocks right of
+            // it another: every extra slab is another pass over y (16 B per row), and on banded + random input a
+            // remote block holds about one entry per row (C5 at 8 ranks: 8 passes -> 3)
+            const int r = ctx->rank, W = ctx->world;
+            int n = 0;
+            if (r > 0) { ctx->h_slab_col[n] = 0; ctx->slab_blk_lo[n] = 0; ctx->slab_blk_hi[n] = r; n++; }
+            ctx->own_lo = n;
+            const uint64_t b = ctx->h_row_splits[r], w = ctx->h_row_splits[r + 1] - b;
+            for (int k = 0; k < per_block; k++, n++) { ctx->h_slab_col[n] = (uint32_t)(b + w * k / per_block); ctx->slab_blk_lo[n] = r; ctx->slab_blk_hi[n] = r + 1; }
+            ctx->own_hi = n;
+            if (r + 1 < W) { ctx->h_slab_col[n] = ctx->h_row_splits[r + 1]; ctx->slab_blk_lo[n] = r + 1; ctx->slab_blk_hi[n] = W; n++; }
+            ctx->slabs = n;
+            ctx->h_slab_col[n] = ctx->cols;
+            ctx->slab_cols = 0;
+        } else {
             ctx->slabs = per_block * ctx->world;
             for (int r = 0; r < ctx->world; r++) {
                 const uint64_t b = ctx->h_row_splits[r], w = ctx->h_row_splits[r + 1] - b;
-                for (int k = 0; k < per_block; k++) ctx->h_slab_col[r * per_block + k] = (uint32_t)(b + w * k / per_block);
+                for (int k = 0; k < per_block; k++) {
+                    ctx->h_slab_col[r * per_block + k] = (uint32_t)(b + w * k / per_block);
+                    ctx->slab_blk_lo[r * per_block + k] = r;
+                    ctx->slab_blk_hi[r * per_block + k] = r + 1;
+                }
             }
             ctx->h_slab_col[ctx->slabs] = ctx->cols;
             ctx->own_lo = ctx->rank * per_block;

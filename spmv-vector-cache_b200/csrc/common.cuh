@@ -58,8 +58,9 @@ struct b200spmv_ctx {
     int opt_dcsr_x16 = -1;        // which slabs run spmv_dcsr_kernel: -1 = measured per slab at setup (b2_tune_slab_kernels),
                                   // 0 = never, n > 0 = those with < n/16 entries per non-empty row
     int opt_prefetch_tiles = 148; // kernel 3: L2 bulk prefetch (UBLKPF) of the tile this many CTAs ahead (0 = off)
-    int opt_own_slabs = 0;        // 1: align the slabs with the ranks' blocks of x (set before setup; see own_lo)
-    int opt_exchange = 2;         // with own_slabs: 1 = NCCL all-gather under the own-block slabs, 2 = peer pulls
+    int opt_own_slabs = 0;        // align the slabs with the ranks' blocks of x (set before setup; see own_lo): 1 = every block its own
+                                  // slabs; 2 = the own block, and ONE slab each for all the blocks left and right of it
+    int opt_exchange = 2;         // with own_slabs: 1 = NCCL all-gather under the own-block slabs, 2 = peer pulls, 3 = packed peer pulls
     int opt_pull_streams = 1;     // copy streams the peer pulls are spread over
     int opt_dcsr_maxrow = 64;     // ... and only when no row piece of the slab is longer than this
     int opt_pin_host = 0;         // see reg_ptr
@@ -86,6 +87,9 @@ struct b200spmv_ctx {
     // block of x.  b200spmv_power_iterate then hands b2_spmv_launch an explicit slab order (own block first, the
     // other blocks in the order they arrive) and, per position, an event to wait on before that slab starts.
     int own_lo = 0, own_hi = 0;
+    int slab_blk_lo[64] = {0}, slab_blk_hi[64] = {0};  // with own_slabs: the ranks' blocks [lo, hi) slab s lies in
+    cudaEvent_t ev_upto[64] = {nullptr};    // the first k blocks of the pull order have landed
+    uint32_t *d_splits = nullptr;      // h_row_splits on the device (packed exchange)
     int order_n = 0;                   // == slabs while an order is in force, else 0
     int h_order[64] = {0};             // slab run at position p
     cudaEvent_t slab_wait[64] = {nullptr};  // by position; nullptr = no wait
@@ -96,7 +100,24 @@ struct b200spmv_ctx {
     void *x_peer[64] = {nullptr};      // the other ranks' d_x, mapped through CUDA IPC
     bool peers_open = false, peers_failed = false;
     int exchange_mode = 0;             // what the last power iteration did: 0 after the step (NCCL), 1 all-gather
-                                       // under the own-block slabs, 2 peer pulls block by block
+                                       // under the own-block slabs, 2 peer pulls block by block, 3 packed peer pulls
+    // exchange 3, packed blocks (multi.cu open_packed): a rank gathers only from the columns its rows reference, so
+    // the owner of a block packs x[those columns] per peer and the peer pulls the packed block; the remote slabs
+    // then index the packed block through a renumbered copy of colind
+    bool packed_ready = false, packed_failed = false;
+    bool packed_active = false;        // this launch: remote slabs read colind_packed / d_unpack
+    uint32_t *colind_packed = nullptr; // csr.colind with the remote slabs' columns renumbered (flags kept)
+    uint64_t *d_unpack = nullptr;      // the packed blocks of the other ranks as pulled: block r at unpack_off[r]
+    uint64_t unpack_off[65] = {0}, need_cnt[64] = {0};  // (colind_packed holds positions in the whole of d_unpack)
+    uint64_t *d_unpack_off = nullptr;
+    uint64_t *d_pack = nullptr;        // my block packed for each peer: for rank r at pack_off[r], pack_cnt[r] values
+    uint64_t pack_off[65] = {0}, pack_cnt[64] = {0};
+    uint64_t *d_pack_off = nullptr;    // pack_off on the device (pack kernel argument)
+    uint32_t *d_pack_bits = nullptr;   // [world][pack_words]: bit c of row r = rank r needs column own_begin + c
+    uint32_t *d_pack_pref = nullptr;   // exclusive prefix of its popcounts
+    uint32_t pack_words = 0;
+    void *pack_peer[64] = {nullptr};   // the other ranks' d_pack (CUDA IPC)
+    uint64_t peer_pack_off[64] = {0};  // where MY packed block starts inside rank r's d_pack
     uint32_t h_ftile_base[65] = {0};   // flagged-kernel tiles per slab (prefix)
     uint64_t h_slab_off[65] = {0};     // entry offset of each slab in colind/vals (padded to FLAG_TILE)
     uint32_t h_slab_nnz[64] = {0};
@@ -239,6 +260,7 @@ int b2_synth_build_csc(b200spmv_ctx *ctx, int kind, uint32_t npr, uint64_t seed)
 int b2_synth_fill_x(b200spmv_ctx *ctx, uint64_t seed);
 // multi.cu
 int b2_comm_destroy(b200spmv_ctx *ctx);
+void b2_close_packed(b200spmv_ctx *ctx);
 void b2_close_peers(b200spmv_ctx *ctx);
 int b2_shard_csc(b200spmv_ctx *ctx, uint32_t index_mask);
 void b2_exec_x_block(const b200spmv_ctx *ctx, int r, uint64_t *lo, uint64_t *hi);

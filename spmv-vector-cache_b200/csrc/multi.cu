@@ -152,6 +152,73 @@ __global__ void scale_into_x_kernel(const uint64_t *__restrict__ y, uint64_t n, 
         else x[i] = (uint64_t)__double_as_longlong(__longlong_as_double((long long)y[i]) / nrm);
     }
 }
+// ---- packed exchange (exchange 3) ----------------------------------------------------------------
+// which rank's block column c lies in (splits[0..world], ascending)
+__device__ __forceinline__ int block_of(const uint32_t *__restrict__ splits, int world, uint32_t c)
+{
+    int lo = 0, hi = world - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(splits + mid) <= c) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+// bit (c - first column of c's block) of that block's plane = some entry of this slab gathers column c
+__global__ void need_mark_kernel(const uint32_t *__restrict__ colind, uint64_t n, const uint32_t *__restrict__ splits, int world,
+                                 uint32_t words, uint32_t *__restrict__ bits)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint32_t g = colind[i] & 0x7FFFFFFFu;
+        const int r = block_of(splits, world, g);
+        const uint32_t c = g - __ldg(splits + r);
+        atomicOr(&bits[(size_t)r * words + (c >> 5)], 1u << (c & 31));
+    }
+}
+__global__ void popc_kernel(const uint32_t *__restrict__ bits, uint64_t n, uint32_t *__restrict__ out)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = __popc(bits[i]);
+}
+// column -> position in d_unpack: start of its block's packed copy + rank among the block's needed columns
+// (row-start flag kept); pads -> position 0 of the slab's first block
+__global__ void remap_packed_kernel(uint32_t *__restrict__ colind, uint64_t nreal, uint64_t ntotal, const uint32_t *__restrict__ splits,
+                                    int world, uint32_t words, const uint32_t *__restrict__ bits, const uint32_t *__restrict__ pref,
+                                    const uint64_t *__restrict__ unpack_off, uint32_t pad_pos)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < ntotal; i += stride) {
+        const uint32_t v = colind[i];
+        uint32_t pos = pad_pos;
+        if (i < nreal) {
+            const uint32_t g = v & 0x7FFFFFFFu;
+            const int r = block_of(splits, world, g);
+            const uint32_t c = g - __ldg(splits + r), w = c >> 5;
+            const size_t k = (size_t)r * words + w;
+            pos = (uint32_t)unpack_off[r] + pref[k] + __popc(bits[k] & ((1u << (c & 31)) - 1u));
+        }
+        colind[i] = (v & 0x80000000u) | pos;
+    }
+}
+// One warp per 32 columns of the rank's own block: lane = column.  For every peer whose bitmap has the lane's bit
+// the value goes to that peer's packed block, at (prefix of the word) + (set bits below the lane).
+__global__ void __launch_bounds__(256) pack_kernel(const uint64_t *__restrict__ xb, uint32_t width, int world, int rank,
+                                                   const uint32_t *__restrict__ bits, const uint32_t *__restrict__ pref,
+                                                   uint32_t words, uint64_t *__restrict__ pack, const uint64_t *__restrict__ pack_off)
+{
+    const uint32_t lane = threadIdx.x & 31, below = (1u << lane) - 1u;
+    const uint32_t nwarps = gridDim.x * (blockDim.x >> 5);
+    for (uint32_t w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < words; w += nwarps) {
+        const uint32_t c = w * 32 + lane;
+        const uint64_t xv = c < width ? xb[c] : 0ull;
+        for (int r = 0; r < world; r++) {
+            if (r == rank) continue;
+            const uint32_t b = __ldg(bits + (size_t)r * words + w);
+            if (b >> lane & 1u) pack[pack_off[r] + __ldg(pref + (size_t)r * words + w) + __popc(b & below)] = xv;
+        }
+    }
+}
+
 __global__ void fill_const_kernel(uint64_t *__restrict__ x, uint64_t n, uint64_t bits)
 {
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -342,6 +409,149 @@ void b2_close_peers(b200spmv_ctx *ctx)
     ctx->peers_failed = false;
 }
 
+void b2_close_packed(b200spmv_ctx *ctx)
+{
+    for (int r = 0; r < 64; r++)
+        if (ctx->pack_peer[r]) { cudaIpcCloseMemHandle(ctx->pack_peer[r]); ctx->pack_peer[r] = nullptr; }
+    b2_free(ctx->colind_packed); b2_free(ctx->d_unpack); b2_free(ctx->d_pack); b2_free(ctx->d_pack_off);
+    b2_free(ctx->d_unpack_off); b2_free(ctx->d_splits);
+    b2_free(ctx->d_pack_bits); b2_free(ctx->d_pack_pref);
+    ctx->packed_ready = ctx->packed_failed = ctx->packed_active = false;
+}
+
+// Packed exchange, built once per matrix (own_slabs layout, peers already mapped):
+//  1. mark, per remote block, the columns this rank's entries gather (bitmap over the block);
+//  2. all-gather the bitmaps: the owner of a block learns what every peer needs of it;
+//  3. prefix sums of the popcounts on both sides give a column's position in the packed block;
+//  4. a second copy of colind with the remote slabs renumbered to those positions;
+//  5. send buffers (mapped by the peers through CUDA IPC) and receive buffers.
+// Any failure to map leaves packed_failed set and the caller falls back to whole-block pulls.
+static int open_packed(b200spmv_ctx *ctx)
+{
+    if (ctx->packed_ready || ctx->packed_failed) return 0;
+    cudaStream_t s = ctx->stream;
+    const int W = ctx->world;
+    uint32_t words = 0;
+    for (int r = 0; r < W; r++) words = std::max(words, b2_div_up(ctx->h_row_splits[r + 1] - ctx->h_row_splits[r], 32));
+    words = (words + 1) & ~1u;  // travels as 64-bit words
+    ctx->pack_words = words;
+    const size_t plane = (size_t)W * words;
+    uint32_t *need_bits = nullptr, *need_pref = nullptr, *all_bits = nullptr;
+    uint64_t *d_tab = nullptr;
+    int rc = 0;
+#define PK_TRY(x) do { rc = (x); if (rc) goto done; } while (0)
+#define PK_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { ctx->err = cudaGetErrorString(e_); ctx->cuda_error = (int)e_; rc = B200SPMV_ECUDA; goto done; } } while (0)
+    {
+        PK_TRY(b2_alloc(ctx, &need_bits, plane));
+        PK_TRY(b2_alloc(ctx, &need_pref, plane));
+        PK_TRY(b2_alloc(ctx, &all_bits, plane * W));
+        PK_TRY(b2_alloc(ctx, &ctx->d_pack_bits, plane));
+        PK_TRY(b2_alloc(ctx, &ctx->d_pack_pref, plane));
+        PK_TRY(b2_alloc(ctx, &d_tab, (size_t)W * W + 8 * W));
+        PK_TRY(b2_alloc(ctx, &ctx->d_splits, (size_t)W + 1));
+        PK_CUDA(cudaMemcpyAsync(ctx->d_splits, ctx->h_row_splits, ((size_t)W + 1) * 4, cudaMemcpyHostToDevice, s));
+        PK_CUDA(cudaMemsetAsync(need_bits, 0, plane * 4, s));
+        for (int sl = 0; sl < ctx->slabs; sl++) {
+            if ((sl >= ctx->own_lo && sl < ctx->own_hi) || ctx->h_slab_nnz[sl] == 0) continue;
+            need_mark_kernel<<<ctx->sms * 8, 256, 0, s>>>(ctx->csr.colind + ctx->h_slab_off[sl], ctx->h_slab_nnz[sl], ctx->d_splits, W,
+                                                          words, need_bits);
+        }
+        PK_CUDA(cudaGetLastError());
+        // rank q's bitmap of block r lands at all_bits[q][r]; mine to pack from are all_bits[q][rank]
+        PK_CUDA(cudaMemcpyAsync(all_bits + (size_t)ctx->rank * plane, need_bits, plane * 4, cudaMemcpyDeviceToDevice, s));
+        if (g_nccl.allgather(all_bits + (size_t)ctx->rank * plane, all_bits, plane / 2, NCCL_UINT64, ctx->comm, s) != 0) { rc = b2_fail(ctx, B200SPMV_ENCCL, "ncclAllGather of the column bitmaps failed"); goto done; }
+        for (int q = 0; q < W; q++)
+            PK_CUDA(cudaMemcpyAsync(ctx->d_pack_bits + (size_t)q * words, all_bits + (size_t)q * plane + (size_t)ctx->rank * words,
+                                    (size_t)words * 4, cudaMemcpyDeviceToDevice, s));
+        PK_CUDA(cudaMemsetAsync(ctx->d_pack_bits + (size_t)ctx->rank * words, 0, (size_t)words * 4, s));
+        // prefix sums, block by block, on both sides; totals = last prefix + last popcount
+        std::vector<uint32_t> last(4 * W);
+        for (int side = 0; side < 2; side++) {
+            const uint32_t *bits = side ? ctx->d_pack_bits : need_bits;
+            uint32_t *pref = side ? ctx->d_pack_pref : need_pref;
+            popc_kernel<<<b2_div_up(plane, 256), 256, 0, s>>>(bits, plane, pref);
+            PK_CUDA(cudaGetLastError());
+            for (int r = 0; r < W; r++) {
+                PK_CUDA(cudaMemcpyAsync(&last[side * 2 * W + r], pref + (size_t)r * words + words - 1, 4, cudaMemcpyDeviceToHost, s));
+                PK_TRY(b2_exclusive_scan_u32(ctx, pref + (size_t)r * words, words, s));
+                PK_CUDA(cudaMemcpyAsync(&last[side * 2 * W + W + r], pref + (size_t)r * words + words - 1, 4, cudaMemcpyDeviceToHost, s));
+            }
+        }
+        PK_CUDA(cudaStreamSynchronize(s));
+        uint64_t uoff = 0, poff = 0;
+        for (int r = 0; r < W; r++) {
+            ctx->need_cnt[r] = (uint64_t)last[r] + last[W + r];
+            ctx->pack_cnt[r] = (uint64_t)last[2 * W + r] + last[3 * W + r];
+            ctx->unpack_off[r] = uoff;
+            ctx->pack_off[r] = poff;
+            uoff += (ctx->need_cnt[r] + 32 + 31) & ~31ull;  // 256-byte aligned, never empty (pads gather position 0)
+            poff += (ctx->pack_cnt[r] + 32 + 31) & ~31ull;
+        }
+        ctx->unpack_off[W] = uoff;
+        ctx->pack_off[W] = poff;
+        PK_TRY(b2_alloc(ctx, &ctx->d_unpack, uoff));
+        PK_TRY(b2_alloc(ctx, &ctx->d_pack, poff));
+        if (uoff >= (1ull << 31)) { rc = b2_fail(ctx, B200SPMV_EINVAL, "packed blocks must stay below 2^31 values"); goto done; }
+        PK_TRY(b2_alloc(ctx, &ctx->d_pack_off, (size_t)W + 1));
+        PK_TRY(b2_alloc(ctx, &ctx->d_unpack_off, (size_t)W + 1));
+        PK_CUDA(cudaMemsetAsync(ctx->d_unpack, 0, uoff * 8, s));
+        PK_CUDA(cudaMemsetAsync(ctx->d_pack, 0, poff * 8, s));
+        PK_CUDA(cudaMemcpyAsync(ctx->d_pack_off, ctx->pack_off, ((size_t)W + 1) * 8, cudaMemcpyHostToDevice, s));
+        PK_CUDA(cudaMemcpyAsync(ctx->d_unpack_off, ctx->unpack_off, ((size_t)W + 1) * 8, cudaMemcpyHostToDevice, s));
+        // the renumbered copy of colind
+        PK_TRY(b2_alloc(ctx, &ctx->colind_packed, (size_t)ctx->padded_nnz));
+        PK_CUDA(cudaMemcpyAsync(ctx->colind_packed, ctx->csr.colind, (size_t)ctx->padded_nnz * 4 + 256, cudaMemcpyDeviceToDevice, s));
+        for (int sl = 0; sl < ctx->slabs; sl++) {
+            if (sl >= ctx->own_lo && sl < ctx->own_hi) continue;
+            remap_packed_kernel<<<ctx->sms * 8, 256, 0, s>>>(ctx->colind_packed + ctx->h_slab_off[sl], ctx->h_slab_nnz[sl],
+                                                             ctx->h_slab_off[sl + 1] - ctx->h_slab_off[sl], ctx->d_splits, W, words,
+                                                             need_bits, need_pref, ctx->d_unpack_off,
+                                                             (uint32_t)ctx->unpack_off[ctx->slab_blk_lo[sl]]);
+        }
+        PK_CUDA(cudaGetLastError());
+        // every rank's table of offsets and counts, and the IPC handle of its send buffer
+        uint64_t *mine = d_tab + (size_t)ctx->rank * (W + 8);
+        std::vector<uint64_t> row(W + 8, 0), tab((size_t)W * (W + 8));
+        for (int r = 0; r < W; r++) row[r] = ctx->pack_off[r] << 32 | ctx->pack_cnt[r];
+        cudaIpcMemHandle_t h;
+        memset(&h, 0, sizeof h);
+        const bool got = cudaIpcGetMemHandle(&h, ctx->d_pack) == cudaSuccess;
+        if (!got) { cudaGetLastError(); memset(&h, 0, sizeof h); }
+        memcpy(&row[W], &h, 64);
+        PK_CUDA(cudaMemcpyAsync(mine, row.data(), (size_t)(W + 8) * 8, cudaMemcpyHostToDevice, s));
+        if (g_nccl.allgather(mine, d_tab, (size_t)W + 8, NCCL_UINT64, ctx->comm, s) != 0) { rc = b2_fail(ctx, B200SPMV_ENCCL, "ncclAllGather of the pack tables failed"); goto done; }
+        PK_CUDA(cudaMemcpyAsync(tab.data(), d_tab, tab.size() * 8, cudaMemcpyDeviceToHost, s));
+        PK_CUDA(cudaStreamSynchronize(s));
+        uint64_t ok = got ? 1 : 0;
+        const cudaIpcMemHandle_t zero = {};
+        for (int r = 0; r < W && ok; r++) {
+            if (r == ctx->rank) continue;
+            const uint64_t *t = &tab[(size_t)r * (W + 8)];
+            ctx->peer_pack_off[r] = t[ctx->rank] >> 32;
+            if ((t[ctx->rank] & 0xFFFFFFFFull) != ctx->need_cnt[r]) { ok = 0; break; }  // both sides must count the same columns
+            cudaIpcMemHandle_t ph;
+            memcpy(&ph, &t[W], 64);
+            if (memcmp(&ph, &zero, 64) == 0 || cudaIpcOpenMemHandle(&ctx->pack_peer[r], ph, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                ctx->pack_peer[r] = nullptr;
+                ok = 0;
+            }
+        }
+        PK_CUDA(cudaMemcpyAsync(d_tab, &ok, 8, cudaMemcpyHostToDevice, s));
+        if (g_nccl.allreduce(d_tab, d_tab, 1, NCCL_UINT64, NCCL_SUM, ctx->comm, s) != 0) { rc = b2_fail(ctx, B200SPMV_ENCCL, "ncclAllReduce failed"); goto done; }
+        uint64_t n_ok = 0;
+        PK_CUDA(cudaMemcpyAsync(&n_ok, d_tab, 8, cudaMemcpyDeviceToHost, s));
+        PK_CUDA(cudaStreamSynchronize(s));
+        if (n_ok == (uint64_t)W) ctx->packed_ready = true;
+    }
+done:
+#undef PK_TRY
+#undef PK_CUDA
+    b2_free(need_bits); b2_free(need_pref); b2_free(all_bits); b2_free(d_tab);
+    if (rc || !ctx->packed_ready) { b2_close_packed(ctx); ctx->packed_failed = true; }
+    return rc;
+}
+
 extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_current_x, int flags,
                                       float *ms_total, double *last_norm)
 {
@@ -384,29 +594,50 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
         for (int r = 0; r < W; r++) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_blk[r], cudaEventDisableTiming));
     }
     int mode = overlap ? ctx->opt_exchange : 0;
-    if (mode == 2) { B2_TRY(open_peers(ctx)); if (!ctx->peers_open) mode = 1; }
+    if (mode >= 2) { B2_TRY(open_peers(ctx)); if (!ctx->peers_open) mode = 1; }
+    if (mode == 3) { B2_TRY(open_packed(ctx)); if (!ctx->packed_ready) mode = 2; }
     ctx->exchange_mode = mode;
     cudaStream_t xs = overlap ? ctx->comm_stream : s;
-    if (overlap) {  // own block first, then the blocks of ranks rank+1, rank+2, ... (the order the pulls are issued in)
+    // Slab order: own block first, then the other slabs by the place of their first block in the pull order (rank+1,
+    // rank+2, ...); a slab may start once the LAST of its blocks in that order has landed (wait_k).
+    int wait_k[64] = {0};
+    if (overlap) {
         int pos = 0;
-        for (int k = 0; k < W; k++) {
-            const int r = (ctx->rank + k) % W;
-            for (int j = 0; j < per_block; j++) ctx->h_order[pos++] = r * per_block + j;
+        for (int sl = ctx->own_lo; sl < ctx->own_hi; sl++) ctx->h_order[pos++] = sl;
+        std::vector<std::pair<int, int>> rest;  // (first place in the pull order, slab)
+        for (int sl = 0; sl < ctx->slabs; sl++) {
+            if (sl >= ctx->own_lo && sl < ctx->own_hi) continue;
+            int first = W, last = 0;
+            for (int b = ctx->slab_blk_lo[sl]; b < ctx->slab_blk_hi[sl]; b++) {
+                const int k = (b - ctx->rank + W) % W;
+                first = std::min(first, k);
+                last = std::max(last, k);
+            }
+            rest.push_back(std::make_pair(first, sl));
+            wait_k[sl] = last;
         }
+        std::sort(rest.begin(), rest.end());
+        for (auto &p : rest) ctx->h_order[pos++] = p.second;
+        for (int k = 0; k < W; k++)
+            if (!ctx->ev_upto[k]) B2_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_upto[k], cudaEventDisableTiming));
     }
     uint64_t *barrier_word = (uint64_t *)(ctx->d_norm + 4);
-    bool in_flight = false;
+    bool in_flight = false, packed_in_flight = false;
     B2_CHECK(ctx, cudaEventRecord(ctx->ev0, s));
     for (int it = 0; it < steps; it++) {
         if (overlap) {
             for (int pos = 0; pos < ctx->slabs; pos++) ctx->slab_wait[pos] = nullptr;
             if (in_flight && mode == 1) ctx->slab_wait[per_block] = ctx->ev_xdone;
-            if (in_flight && mode == 2)
-                for (int k = 1; k < W; k++) ctx->slab_wait[k * per_block] = ctx->ev_blk[(ctx->rank + k) % W];
+            if (in_flight && mode >= 2)
+                for (int pos = per_block; pos < ctx->slabs; pos++) ctx->slab_wait[pos] = ctx->ev_upto[wait_k[ctx->h_order[pos]]];
             ctx->order_n = ctx->slabs;
         }
+        // exchange 3: the previous step left the other blocks PACKED (only the columns this rank gathers); the whole
+        // x is there before the first step and again after the last (which pulls whole blocks)
+        ctx->packed_active = packed_in_flight;
         const int rc = b2_spmv_launch(ctx, spmv_flags, s);
         ctx->order_n = 0;
+        ctx->packed_active = false;
         if (rc) return rc;
         if (!is_u64) {
             sumsq_partial_kernel<<<RED_BLOCKS, RED_THREADS, 0, s>>>((const double *)yb, ctx->local_rows, partial);
@@ -414,10 +645,18 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
             if (ctx->world > 1) NCCL_TRY(ctx, g_nccl.allreduce(norm2, norm2, 1, NCCL_FLOAT64, NCCL_SUM, ctx->comm, s));
         }
         // peer pulls, u64 (no norm to agree on): nobody overwrites its block before everybody has pulled it
-        if (mode == 2 && is_u64) NCCL_TRY(ctx, g_nccl.allreduce(barrier_word + 1, barrier_word + 1, 1, NCCL_UINT64, NCCL_SUM, ctx->comm, s));
+        if (mode >= 2 && is_u64) NCCL_TRY(ctx, g_nccl.allreduce(barrier_word + 1, barrier_word + 1, 1, NCCL_UINT64, NCCL_SUM, ctx->comm, s));
         scale_into_x_kernel<<<ctx->sms * 8, 256, 0, s>>>(yb, ctx->local_rows, norm2, is_u64, xb);
         ctx->launches += is_u64 ? 1 : 3;
-        const bool timed = it == steps - 1 && ctx->world > 1;  // exchange time of the last step -> stat "xchgtime_ns"
+        const bool packed_now = mode == 3 && it < steps - 1;
+        if (packed_now) {  // my block, packed once per peer (the buffers the peers pull from)
+            pack_kernel<<<ctx->sms * 8, 256, 0, s>>>(xb, ctx->local_rows, W, ctx->rank, ctx->d_pack_bits, ctx->d_pack_pref, ctx->pack_words,
+                                                      ctx->d_pack, ctx->d_pack_off);
+            B2_CHECK(ctx, cudaGetLastError());
+            ctx->launches += 1;
+        }
+        // exchange time of a representative step -> stat "xchgtime_ns" (packed: the last packed one, else the last)
+        const bool timed = ctx->world > 1 && (mode == 3 && steps > 1 ? it == steps - 2 : it == steps - 1);
         if (overlap) {
             B2_CHECK(ctx, cudaEventRecord(ctx->ev_xready, s));
             B2_CHECK(ctx, cudaStreamWaitEvent(xs, ctx->ev_xready, 0));
@@ -426,7 +665,7 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
             if (!ctx->ev_x0) { B2_CHECK(ctx, cudaEventCreate(&ctx->ev_x0)); B2_CHECK(ctx, cudaEventCreate(&ctx->ev_x1)); }
             B2_CHECK(ctx, cudaEventRecord(ctx->ev_x0, xs));
         }
-        if (mode == 2) {
+        if (mode >= 2) {
             // every rank's block is written once this all-reduce has gone round; the next step's norm all-reduce
             // (after every rank's last slab, hence after its pulls) is what lets a rank overwrite its block again
             NCCL_TRY(ctx, g_nccl.allreduce(barrier_word, barrier_word, 1, NCCL_UINT64, NCCL_SUM, ctx->comm, xs));
@@ -437,11 +676,16 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
                 const int r = (ctx->rank + k) % W;
                 const size_t b = ctx->h_row_splits[r], e = ctx->h_row_splits[r + 1];
                 cudaStream_t ps = ctx->pull_stream[(k - 1) % ns];
-                if (e > b)
+                if (packed_now) {
+                    if (ctx->need_cnt[r])
+                        B2_CHECK(ctx, cudaMemcpyAsync(ctx->d_unpack + ctx->unpack_off[r], (const uint64_t *)ctx->pack_peer[r] + ctx->peer_pack_off[r],
+                                                      ctx->need_cnt[r] * 8, cudaMemcpyDefault, ps));
+                } else if (e > b)
                     B2_CHECK(ctx, cudaMemcpyAsync((uint64_t *)ctx->d_x + b, (const uint64_t *)ctx->x_peer[r] + b, (e - b) * 8,
                                                   cudaMemcpyDefault, ps));
                 B2_CHECK(ctx, cudaEventRecord(ctx->ev_blk[r], ps));
                 B2_CHECK(ctx, cudaStreamWaitEvent(xs, ctx->ev_blk[r], 0));
+                B2_CHECK(ctx, cudaEventRecord(ctx->ev_upto[k], xs));  // blocks rank+1 .. rank+k are all here
             }
         } else {
             B2_TRY(allgather_x(ctx, xs));
@@ -450,6 +694,7 @@ extern "C" int b200spmv_power_iterate(b200spmv_ctx *ctx, int steps, int use_curr
         if (overlap) {
             B2_CHECK(ctx, cudaEventRecord(ctx->ev_xdone, xs));
             in_flight = true;
+            packed_in_flight = packed_now;
         }
     }
     if (in_flight) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_xdone, 0));  // x is whole again when the call returns

@@ -778,7 +778,7 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
     const bool strict = (flags & B200SPMV_STRICT_ORDER) || !ctx->flagged;
     const bool persist = !(flags & B200SPMV_NO_PERSIST);
     const bool accumulate = flags & B200SPMV_ACCUMULATE;
-    const uint64_t *x = (const uint64_t *)ctx->d_x;
+    const uint64_t *xfull = (const uint64_t *)ctx->d_x;
     uint64_t *y = (uint64_t *)ctx->d_y + ctx->row_begin;
     const uint64_t *vals = (const uint64_t *)m.vals;
     const size_t stride = ctx->rowptr_stride;
@@ -796,15 +796,15 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
             const uint64_t b0 = (uint64_t)ctx->h_slab_col[sl] * 8 & ~15ull, b1 = ((uint64_t)ctx->h_slab_col[sl + 1] * 8 + 15) & ~15ull;
             if (b1 > b0 && (double)(b1 - b0) <= 0.6 * (double)ctx->l2_bytes) {
                 const uint64_t nthr = (b1 - b0 + XPF_CHUNK - 1) / XPF_CHUNK;
-                x_prefetch_kernel<<<(unsigned)((nthr + 127) / 128), 128, 0, s>>>((const char *)x + b0, b1 - b0);
+                x_prefetch_kernel<<<(unsigned)((nthr + 127) / 128), 128, 0, s>>>((const char *)xfull + b0, b1 - b0);
                 ctx->launches += 1;
             }
         }
         if (ctx->wait_slab_events) B2_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_slab[sl], 0));
         if (strict) {
             const unsigned grid = b2_div_up(rows, 256);
-            if (read_y) spmv_rowseq_kernel<DT, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows, ctx->colmask);
-            else spmv_rowseq_kernel<DT, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, rows, ctx->colmask);
+            if (read_y) spmv_rowseq_kernel<DT, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, xfull, y, rows, ctx->colmask);
+            else spmv_rowseq_kernel<DT, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, xfull, y, rows, ctx->colmask);
             ctx->launches += 1;
             B2_CHECK(ctx, cudaGetLastError());
             continue;
@@ -813,7 +813,11 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
         const uint32_t nt = ctx->h_ftile_base[sl + 1] - tb;
         const bool has_empty = ctx->h_nseg[sl] < rows;
         if (!read_y && has_empty) B2_CHECK(ctx, cudaMemsetAsync(y, 0, (size_t)rows * 8, s));  // rows no flag will touch
-        const uint32_t *ci = m.colind + ctx->h_slab_off[sl];
+        // packed exchange (multi.cu): a slab of another rank's block reads the packed block through the renumbered indices
+        const bool packed = ctx->packed_active && ordered && (sl < ctx->own_lo || sl >= ctx->own_hi);
+        const uint32_t *colbase = packed ? ctx->colind_packed : m.colind;
+        const uint64_t *x = packed ? ctx->d_unpack : xfull;
+        const uint32_t *ci = colbase + ctx->h_slab_off[sl];
         const uint64_t *va = vals + ctx->h_slab_off[sl];
         const uint32_t *segrow = m.seg_row + sl * stride, *tseg = m.tile_seg + tb + sl;
         const bool prof = prof_begin(ctx, s);
@@ -823,11 +827,11 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
         if (dcsr_slab(ctx, sl)) {
             const unsigned grid = b2_div_up(nseg, 256);
             if (persist) {
-                if (read_y) spmv_dcsr_kernel<DT, true, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
-                else spmv_dcsr_kernel<DT, true, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+                if (read_y) spmv_dcsr_kernel<DT, true, true><<<grid, 256, 0, s>>>(rowptr, colbase, vals, x, y, segrow, nseg, ctx->colmask);
+                else spmv_dcsr_kernel<DT, true, false><<<grid, 256, 0, s>>>(rowptr, colbase, vals, x, y, segrow, nseg, ctx->colmask);
             } else {
-                if (read_y) spmv_dcsr_kernel<DT, false, true><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
-                else spmv_dcsr_kernel<DT, false, false><<<grid, 256, 0, s>>>(rowptr, m.colind, vals, x, y, segrow, nseg, ctx->colmask);
+                if (read_y) spmv_dcsr_kernel<DT, false, true><<<grid, 256, 0, s>>>(rowptr, colbase, vals, x, y, segrow, nseg, ctx->colmask);
+                else spmv_dcsr_kernel<DT, false, false><<<grid, 256, 0, s>>>(rowptr, colbase, vals, x, y, segrow, nseg, ctx->colmask);
             }
             if (prof) prof_end(ctx, s);
             ctx->launches += 1;

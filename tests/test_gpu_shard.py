@@ -74,9 +74,11 @@ def test_synthetic_sharded_equals_whole(kind, rows, npr):
 
 @pytest.mark.parametrize("name,dtype,world,slabs", [("circuit204", "u64", 3, 0), ("circuit204", "f64", 2, 4), ("i64k", "u64", 8, 0),
                                                     ("i64k", "f64", 4, 6)])
-def test_slabs_aligned_with_the_ranks_blocks(oracle, name, dtype, world, slabs):
+@pytest.mark.parametrize("layout", [1, 2])
+def test_slabs_aligned_with_the_ranks_blocks(oracle, name, dtype, world, slabs, layout):
     """option own_slabs: the column slabs follow the ranks' blocks of x (what lets the iterated SpMV overlap the
-    exchange); a single SpMV over such slabs must still be the reference product, strict order included."""
+    exchange; layout 2: one slab each for everything left and right of the own block); a single SpMV over such
+    slabs must still be the reference product, strict order included."""
     import b200spmv as b2
     m = H.load_matrix_dir(os.path.join(H.MATRICES, name))
     vals = H.rand_values(m.nnz, dtype, 31)
@@ -90,11 +92,15 @@ def test_slabs_aligned_with_the_ranks_blocks(oracle, name, dtype, world, slabs):
             e = b2.Engine(0)
             e.set_option("world", world)
             e.set_option("rank", r)
-            e.set_option("own_slabs", 1)
+            e.set_option("own_slabs", layout)
             if slabs:
                 e.set_option("slabs", slabs)
             e.setup_csc(m.rows, m.cols, m.colptr, m.rowind, vals, b2.U64 if dtype == "u64" else b2.F64)
-            assert e.stat("slabs") % world == 0
+            if layout == 1:
+                assert e.stat("slabs") % world == 0
+            else:
+                per = max(1, -(-slabs // world)) if slabs else None
+                assert per is None or e.stat("slabs") == per + (r > 0) + (r < world - 1)
             e.exec(x, y, flags)
             e.close()
         if dtype == "u64" or flags & b2.STRICT_ORDER:

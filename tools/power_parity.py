@@ -2,7 +2,8 @@
 """Iterated SpMV over several GPUs against the same iteration on one GPU (run under torchrun, >= 2 ranks).
 
 Every rank builds its row block of a banded+random matrix (a) with the slabs aligned to the ranks' x blocks and
-the other blocks pulled from the peers block by block under the slabs (exchange 2), (b) the same with one NCCL
+the other blocks pulled from the peers block by block under the slabs (exchange 2; exchange 3: the same with PACKED
+blocks -- only the columns the pulling rank gathers), (b) the same with one NCCL
 all-gather under the own-block slabs (exchange 1), (c) with the all-gather after the step, and (d) the whole matrix
 alone.  After K steps the replicated x of (a)-(c) must equal the x of (d): bit for bit for uint64, to 1e-12 relative for fp64 (the slabs are summed in another order).
 """
@@ -29,7 +30,7 @@ def make(local, rank, world, dtype, rows, npr, slabs, own, exchange=2):
         dist.broadcast(uid, 0)
         e.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
         if own:
-            e.set_option("own_slabs", 1)
+            e.set_option("own_slabs", int(own))  # 1: every block its own slabs; 2: own block + one slab left, one right
             e.set_option("exchange", exchange)
     if slabs:
         e.set_option("slabs", slabs)
@@ -51,7 +52,7 @@ def main():
             single.power_iterate(steps, False, 0)
             want = single.get_x()
             del single
-            for own, exchange in ((True, 2),) if quick else ((True, 2), (True, 1), (False, 0)):
+            for own, exchange in ((2, 3), (1, 2)) if quick else ((2, 3), (1, 3), (2, 2), (1, 2), (2, 1), (1, 1), (0, 0)):
                 e = make(local, rank, world, dtype, rows, 5, slabs, own, exchange)
                 # two calls: the second continues from the replicated x (what bench.py does after its warm-up)
                 e.power_iterate(steps // 2, False, 0)
@@ -64,8 +65,8 @@ def main():
                 else:
                     err = float(np.max(np.abs(got - want)) / np.max(np.abs(want)))
                     ok = err < 1e-12
-                print("rank %d %s rows %d slabs opt %d -> %d exchange %d: %s (%s)" %
-                      (rank, name, rows, slabs, e.stat("slabs"), exchange, "ok" if ok else "MISMATCH", err), flush=True)
+                print("rank %d %s rows %d slabs opt %d -> %d own_slabs %d exchange %d: %s (%s)" %
+                      (rank, name, rows, slabs, e.stat("slabs"), int(own), exchange, "ok" if ok else "MISMATCH", err), flush=True)
                 bad += not ok
                 del e
     # b200spmv_exec over several ranks: each rank uploads 1/world of the host x and the rest arrives over NVLink
