@@ -97,6 +97,7 @@ extern "C" int b200spmv_set_option(b200spmv_ctx *ctx, const char *key, int64_t v
     const std::string k(key);
     if (k == "slabs") { if (value < 0 || value > 64) return b2_fail(ctx, B200SPMV_EINVAL, "slabs must be 0..64"); ctx->opt_slabs = (int)value; }
     else if (k == "persist_bytes") ctx->opt_persist_bytes = value;
+    else if (k == "persist") { if (value < -1 || value > 1) return b2_fail(ctx, B200SPMV_EINVAL, "persist must be -1 (measured), 0 or 1"); ctx->opt_persist = (int)value; }
     else if (k == "require_aligned") ctx->opt_require_aligned = (int)value;
     else if (k == "keep_csc") ctx->opt_keep_csc = (int)value;
     else if (k == "kernel") { if (value != 3 && value != 6) return b2_fail(ctx, B200SPMV_EINVAL, "kernel must be 3 or 6"); ctx->opt_kernel = (int)value; }
@@ -138,16 +139,18 @@ static int choose_slabs(const b200spmv_ctx *ctx)
     const double l2 = (double)ctx->l2_bytes;
     if (l2 <= 0 || xbytes <= 0.6 * l2) return 1;
     int s = std::min(64, (int)std::ceil(xbytes / (0.45 * l2)));
-    // Every slab after the first read-modify-writes y once more and shortens the row pieces the kernels
-    // work on.  When an L2-sized slab would hold only a few entries per row (C5: 16 entries per row over 18
-    // slabs; C4: 32 over 9) that costs more than the L2 hits save: keep >= 8 entries per row and slab and
-    // let part of the gathers go to HBM (profiles/r01_c5_shard_sweep.txt, r01_c4_shard_sweep.txt).
-    // (per NON-EMPTY row: the empty rows of a skewed block cost the kernels nothing; profiles/r01_c4_shard_sweep.txt)
+    // Every slab after the first updates y once more and shortens the row pieces the kernels work on.  When an
+    // L2-sized slab would hold only a few entries per row (C5: 16 entries per row over 18 slabs; C4: 32 over 9) that
+    // costs more than the L2 hits save: keep about 16/3 entries per row and slab and let part of the gathers go to HBM.
+    // (per NON-EMPTY row: the empty rows of a skewed block cost the kernels nothing; profiles/r01_c4_shard_sweep.txt.)
+    // Since the kernels close a row with one reduction request instead of a load and a store, short row pieces are
+    // cheaper than in round 1, when the rule was 8 per row and slab: banded(11)+5 at 16 M rows runs 212 / 233 / 242 /
+    // 237 / 207 GNNZ/s with 1 / 2 / 3 / 4 / 6 slabs (profiles/r02_sweep_dcsr.txt) and gets 3.
     const double per_row = ctx->nonempty_rows ? (double)ctx->local_nnz / (double)ctx->nonempty_rows : 0.0;
-    int by_rows = (int)(per_row / 8.0 + 0.5);  // banded(11)+5 has 15.99 per row (short rows at the edges): 2 slabs, 245 vs 210 GNNZ/s
+    int by_rows = (int)(per_row * 3.0 / 16.0 + 0.5);
     // Column skew (R-MAT: 3/4 of the entries sit in the lower half of the columns): most of the uniform slabs
-    // then hold far fewer entries per row than the average says, so fewer of them pay off.
-    if (ctx->upper_half_nnz * 100 < ctx->local_nnz * 35) by_rows = (by_rows * 2 + 2) / 3;
+    // then hold far fewer entries per row than the average says, so fewer of them pay off (8 per row and slab).
+    if (ctx->upper_half_nnz * 100 < ctx->local_nnz * 35) by_rows = (int)(per_row / 8.0 + 0.5), by_rows = (by_rows * 2 + 2) / 3;
     s = std::max(1, std::min(s, by_rows));
     return s;
 }
@@ -632,6 +635,7 @@ extern "C" int b200spmv_stat_u64(b200spmv_ctx *ctx, const char *key, uint64_t *o
         *out = (uint64_t)(ctx->h_slab_dcsr[i] == 1);
     }
     else if (k == "tunetime_ns") *out = ctx->tunetime_ns;
+    else if (k == "persist") *out = (uint64_t)(ctx->opt_persist >= 0 ? ctx->opt_persist != 0 : ctx->persist_tuned);
     else if (k.rfind("slab_ns_", 0) == 0 || k.rfind("slab_nnz_", 0) == 0 || k.rfind("slab_rows_", 0) == 0 || k.rfind("slab_maxrow_", 0) == 0) {
         const int i = atoi(k.c_str() + k.rfind('_') + 1);
         if (i < 0 || i >= ctx->slabs) return b2_fail(ctx, B200SPMV_EINVAL, "no such slab");

@@ -48,6 +48,8 @@ struct b200spmv_ctx {
     // options
     int opt_slabs = 0;            // 0 = auto
     int64_t opt_persist_bytes = 0;  // 0 = device max
+    int opt_persist = -1;         // L2 access-policy window + evict_last on x: -1 = as measured at setup (persist_tuned), 0 = off,
+                                  // 1 = on; flag B200SPMV_NO_PERSIST switches it off for one call whatever this says
     int opt_require_aligned = 0;
     int opt_keep_csc = 0;
     int opt_kernel = 3;           // 3 = flagged segmented sum, one tile per CTA (default); 6 = the same by persistent warps (spmv.cu)
@@ -163,6 +165,8 @@ struct b200spmv_ctx {
     void *reg_ptr[2] = {nullptr, nullptr};
     size_t reg_bytes[2] = {0, 0};
     bool persist_set = false;
+    bool persist_tuned = true;    // what b2_tune_slab_kernels measured (window on unless off is > 1 % faster)
+    int tune_persist = -1;        // during that measurement: 0 / 1 = force
 
     // multi-GPU
     ncclComm *comm = nullptr;

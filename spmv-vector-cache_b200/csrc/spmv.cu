@@ -68,12 +68,26 @@ __device__ __forceinline__ void ld256_u64(const void *p, uint64_t *v)
                  : "l"(p));
 }
 
+// y[row] (+)= v without reading y into the SM: one reduction request (RED.ADD.F64 / .64) instead of a load and a
+// store.  Kernel 3 closes every row at most once per launch (the carries are added by the fix-up launch), so the
+// result is the same y_old + v, bit for bit, as the load-add-store it replaces -- IEEE round-to-nearest on the
+// L2's adder as on the SM's -- and the summation order stays deterministic.
+#ifndef B2_Y_RED
+#define B2_Y_RED 1  // 0: load-add-store (measurement builds: make variant NAME=nored DEFS=-DB2_Y_RED=0)
+#endif
+template <int DT>
+__device__ __forceinline__ void y_reduce(uint64_t *addr, uint64_t v)
+{
+    if (DT == B200SPMV_F64) atomicAdd(reinterpret_cast<double *>(addr), __longlong_as_double((long long)v));
+    else atomicAdd(reinterpret_cast<unsigned long long *>(addr), (unsigned long long)v);
+}
 template <int DT, bool READ_Y, bool HAS_EMPTY>
 __device__ __forceinline__ void store_segment(uint64_t *__restrict__ y, const uint32_t *__restrict__ seg_row,
                                               uint32_t rows, uint32_t seg, uint64_t v)
 {
     const uint32_t row = HAS_EMPTY ? __ldg(seg_row + seg) : seg;
     if (row < rows) {
+        if (READ_Y && B2_Y_RED) { y_reduce<DT>(y + row, v); return; }
         if (READ_Y) v = Semi<DT>::add(y[row], v);
         y[row] = v;
     }
@@ -150,7 +164,7 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
     if (nfl != 0 && segs_before != 0) {
         close_row = HAS_EMPTY ? __ldg(seg_row + segs_before - 1) : segs_before - 1;
         if (close_row >= rows) close_row = NO_ROW;
-        if (READ_Y && close_row != NO_ROW) y_old = y[close_row];
+        if (READ_Y && !B2_Y_RED && close_row != NO_ROW) y_old = y[close_row];
     }
     // a second flag in my entries closes a row that lies wholly inside them: its row id and y are fetched
     // now as well (rows shorter than 8 entries are common once a matrix is cut into column slabs)
@@ -159,7 +173,7 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
     if (nfl > 1) {
         row2 = HAS_EMPTY ? __ldg(seg_row + segs_before) : segs_before;
         if (row2 >= rows) row2 = NO_ROW;
-        if (READ_Y && row2 != NO_ROW) y_old2 = y[row2];
+        if (READ_Y && !B2_Y_RED && row2 != NO_ROW) y_old2 = y[row2];
     }
 
     // branch-free sequential pass: head = sum before my first flag, acc = sum after my last flag
@@ -207,10 +221,13 @@ spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict
         if (close_row != NO_ROW) {  // my first flag closes the row that was open on entry
             uint64_t val = open_left ? Semi<DT>::add(cw, carry_in) : carry_in;
             val = Semi<DT>::add(val, head);
-            if (READ_Y) val = Semi<DT>::add(y_old, val);
-            y[close_row] = val;
+            if (READ_Y && B2_Y_RED) y_reduce<DT>(y + close_row, val);
+            else y[close_row] = READ_Y ? Semi<DT>::add(y_old, val) : val;
         }
-        if (nfl > 1 && row2 != NO_ROW) y[row2] = READ_Y ? Semi<DT>::add(y_old2, mid) : mid;
+        if (nfl > 1 && row2 != NO_ROW) {
+            if (READ_Y && B2_Y_RED) y_reduce<DT>(y + row2, mid);
+            else y[row2] = READ_Y ? Semi<DT>::add(y_old2, mid) : mid;
+        }
         if (nfl > 2) {  // further rows that begin and end inside my entries (very short rows): re-walk
             uint64_t a = 0;
             uint32_t k = 0;
@@ -708,6 +725,15 @@ bool b2_last_slab_chunkable(const b200spmv_ctx *ctx, int flags)
            ctx->order_n == 0 && ctx->local_rows > 0 && !dcsr_slab(ctx, ctx->slabs - 1);
 }
 
+// Is the persisting window (and the evict_last hint on the gathers) on for this call?
+static bool want_persist(const b200spmv_ctx *ctx, int flags)
+{
+    if (flags & B200SPMV_NO_PERSIST) return false;
+    if (ctx->tune_persist >= 0) return ctx->tune_persist != 0;
+    if (ctx->opt_persist >= 0) return ctx->opt_persist != 0;
+    return ctx->persist_tuned;
+}
+
 static int set_persist_window(b200spmv_ctx *ctx, cudaStream_t s, const void *base, size_t bytes, bool on)
 {
     cudaStreamAttrValue attr;
@@ -776,7 +802,7 @@ static int launch_dtype(b200spmv_ctx *ctx, int flags, cudaStream_t s)
 {
     const DeviceCsr &m = ctx->csr;
     const bool strict = (flags & B200SPMV_STRICT_ORDER) || !ctx->flagged;
-    const bool persist = !(flags & B200SPMV_NO_PERSIST);
+    const bool persist = want_persist(ctx, flags);
     const bool accumulate = flags & B200SPMV_ACCUMULATE;
     const uint64_t *xfull = (const uint64_t *)ctx->d_x;
     uint64_t *y = (uint64_t *)ctx->d_y + ctx->row_begin;
@@ -920,6 +946,7 @@ int b2_tune_slab_kernels(b200spmv_ctx *ctx)
     memset(ctx->h_slab_dcsr, 0, sizeof ctx->h_slab_dcsr);
     ctx->tunetime_ns = 0;
     ctx->tune_mask = 0;
+    ctx->persist_tuned = true;
     if (!ctx->flagged || ctx->local_rows == 0) return 0;
     for (int sl = 0; sl < ctx->slabs; sl++) {
         const uint64_t nnz = ctx->h_slab_nnz[sl], nseg = ctx->h_nseg[sl];
@@ -927,9 +954,49 @@ int b2_tune_slab_kernels(b200spmv_ctx *ctx)
         if (nnz < (1u << 18)) ctx->h_slab_dcsr[sl] = nnz < 6 * nseg;  // launch-latency sized: the fixed rule of round 1
         else ctx->tune_mask |= 1ull << sl;
     }
-    if (!ctx->tune_mask || ctx->opt_dcsr_x16 >= 0) return 0;  // nothing to measure / a fixed rule was asked for
     cudaStream_t s = ctx->stream;
     const auto t_begin = std::chrono::steady_clock::now();
+    // The access-policy window first: it keeps more of the gathered slice of x in L2 (profiles/r02_l2_ab.txt) but takes
+    // the set-aside away from y, whose rows the kernels update by reductions in L2.  Measured both ways, three whole
+    // steps at a time (the first untimed), twice each: band, R-MAT and one-slab matrices gain 3-6 % from the window, C3 and short-row
+    // slabs lose 2-6 % (profiles/r02_y_red_ab.txt).  Kept on unless off is more than 1 % faster.
+    ctx->persist_tuned = true;
+    bool ran_persist = false;
+    if (ctx->opt_persist < 0 && ctx->max_persist_bytes > 0 && (uint64_t)ctx->cols * 8 >= (8u << 20) && ctx->local_nnz >= (1u << 22)) {
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        B2_CHECK(ctx, cudaEventCreate(&e0));
+        B2_CHECK(ctx, cudaEventCreate(&e1));
+        float t[2] = {1e30f, 1e30f};
+        int rc = 0;
+        for (int round = 0; round < 4 && !rc; round++) {  // on, off, on, off: the best of two tries each
+            const int on = 1 - (round & 1);
+            ctx->tune_persist = on;
+            ctx->tune_force = 1;
+            rc = b2_spmv_launch(ctx, B200SPMV_ACCUMULATE, s);
+            cudaEventRecord(e0, s);
+            for (int rep = 0; rep < 3 && !rc; rep++) rc = b2_spmv_launch(ctx, B200SPMV_ACCUMULATE, s);
+            cudaEventRecord(e1, s);
+            if (!rc && cudaEventSynchronize(e1) != cudaSuccess) rc = b2_fail(ctx, B200SPMV_ECUDA, "persisting-window measurement failed");
+            float ms = 0.f;
+            if (!rc && cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) t[on] = std::min(t[on], ms);
+        }
+        ctx->tune_persist = -1;
+        ctx->tune_force = 0;
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        if (rc) return rc;
+        ctx->persist_tuned = !(t[0] < 0.99f * t[1]);
+        ran_persist = true;
+    }
+    if (!ctx->tune_mask || ctx->opt_dcsr_x16 >= 0) {  // no slab to measure / a fixed rule was asked for
+        if (ran_persist) {
+            B2_CHECK(ctx, cudaMemsetAsync(ctx->d_y, 0, (size_t)ctx->rows * 8, s));
+            B2_CHECK(ctx, cudaStreamSynchronize(s));
+            ctx->launches = 0;
+            ctx->tunetime_ns = (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t_begin).count();
+        }
+        return 0;
+    }
     const int profile_was = ctx->opt_profile;
     uint64_t best[3][64];
     memset(best, 0xFF, sizeof best);
@@ -983,7 +1050,7 @@ void b2_profile_collect(b200spmv_ctx *ctx)
 // the window only marks x as the data to keep (profiles/r01_gather_paths.txt, A/B).
 int b2_spmv_prepare(b200spmv_ctx *ctx, int flags, cudaStream_t s)
 {
-    const bool persist = !(flags & B200SPMV_NO_PERSIST);
+    const bool persist = want_persist(ctx, flags);
     if (persist != ctx->persist_set) {
         B2_TRY(set_persist_window(ctx, s, ctx->d_x, (size_t)ctx->cols * 8, persist));
         ctx->persist_set = persist;

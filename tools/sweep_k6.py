@@ -31,6 +31,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--quick", action="store_true")
 ap.add_argument("--ablate", action="store_true", help="measurement build: kernel 6 variants only, no result check")
 ap.add_argument("--only", default="")
+ap.add_argument("--variants", default="", help="comma-separated variant names to run (default: all)")
 ap.add_argument("--steps", type=int, default=20)
 args = ap.parse_args()
 
@@ -39,6 +40,7 @@ WORK = [
     ("uniform C3", 0, 1 << 24, 32, [3]),
     ("band16", 3, 1 << 24, 16, [1, 3]),
     ("banded11+5", 2, 1 << 24, 5, [1, 2, 3]),
+    ("uniform 16M x 8", 0, 1 << 24, 8, [3]),
     ("rmat16M", 1, 1 << 24, 32, [0]),
     ("uniform 4M (x in L2)", 0, 1 << 22, 32, [1]),
 ]
@@ -50,6 +52,7 @@ if args.only:
 VARIANTS = [
     ("k3", {"kernel": 3}),
     ("k3 nopersist", {"kernel": 3, "_flags": 4}),
+    ("k3 persist", {"kernel": 3, "persist": 1}),
     ("k3 pf0", {"kernel": 3, "prefetch_tiles": 0}),
     ("k3 pf592", {"kernel": 3, "prefetch_tiles": 592}),
     ("k6 db occ2", {"kernel": 6, "stream_db": 1, "stream_pf": 0, "stream_occ": 0, "stream_vchunks": 1}),
@@ -61,6 +64,8 @@ VARIANTS = [
     ("k6 never dcsr", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1, "dcsr_x16": 0}),
     ("k6 never dcsr nopersist", {"kernel": 6, "stream_db": 0, "stream_pf": 1, "stream_occ": 0, "stream_vchunks": 1, "dcsr_x16": 0, "_flags": 4}),
 ]
+if args.variants:
+    VARIANTS = [v for v in VARIANTS if v[0] in args.variants.split(",")]
 if args.ablate:
     VARIANTS = [v for v in VARIANTS if v[0] in ("k6 db occ2", "k6 nodb occ3", "k6 nodb occ3 pf2")]
 
@@ -76,13 +81,14 @@ for name, kind, rows, npr, slab_list in WORK:
         nnz = e.stat("nz")
         balg = 12 * nnz + 4 * (rows + 1) + 16 * rows
         ns = e.stat("slabs")
-        print("== %s: rows %d nnz %d slabs %d (setup %.2f s) B_alg %.3f GB; per slab nnz/nonempty/maxrow: %s" % (
-            name, rows, nnz, ns, setup_s, balg / 1e9,
+        print("== %s: rows %d nnz %d slabs %d (setup %.2f s, window measured %s) B_alg %.3f GB; per slab nnz/nonempty/maxrow: %s" % (
+            name, rows, nnz, ns, setup_s, "on" if e.stat("persist") else "off", balg / 1e9,
             " ".join("%d/%d/%d" % (e.stat("slab_nnz_%d" % i), e.stat("slab_rows_%d" % i), e.stat("slab_maxrow_%d" % i)) for i in range(ns))),
             flush=True)
         ref = None
         for vname, opts in VARIANTS:
             e.set_option("dcsr_x16", -1)
+            e.set_option("persist", -1)
             e.set_option("prefetch_tiles", 148)
             fl = b2.ACCUMULATE | opts.get("_flags", 0)
             for k, v in opts.items():
