@@ -353,6 +353,9 @@ class Job:
         eng.exec_device(psteps, flags)
         k_ns, k_n = eng.stat("merge_kernel_ns"), eng.stat("merge_kernel_launches")
         slabs = eng.stat("slabs")
+        out["persist_window"] = bool(eng.stat("persist")) and not (flags & b2.NO_PERSIST)
+        out["slab_kernels"] = "".join("d" if eng.stat("slab_dcsr_%d" % i) else "f" for i in range(slabs))
+        out["tune_ms"] = round(eng.stat("tunetime_ns") * 1e-6, 1)
         if args.per_slab:
             out["per_slab"] = [{"ms": round(eng.stat("slab_ns_%d" % i) * 1e-6 / psteps, 4), "nnz": eng.stat("slab_nnz_%d" % i),
                                 "nonempty_rows": eng.stat("slab_rows_%d" % i), "longest_row": eng.stat("slab_maxrow_%d" % i)}
@@ -440,7 +443,8 @@ def run_ours(args):
                 o = job.measure(wl, k_steps, 3, flags, exchange=ex or "pull")
                 o.pop("eng").close()
                 rec = {"workload": o["desc"], "value": o["value"], "unit": "GNNZ/s", "steps": k_steps, "ms_per_step": o["ms_per_step"],
-                       "rows": o["rows"], "nnz": o["nnz"], "slabs": o["slabs"], "setup_s": round(o["setup_s"], 2),
+                       "rows": o["rows"], "nnz": o["nnz"], "slabs": o["slabs"], "persist_window": o["persist_window"], "slab_kernels": o["slab_kernels"],
+                       "setup_s": round(o["setup_s"], 2),
                        "roofline": {k: o["roofline"][k] for k in ("achieved", "peak", "frac", "kernel", "kernel_ms_per_step", "algorithmic_bytes_per_step")}}
                 for k in ("x_exchange_ms_last_step", "exchange", "last_norm"):
                     if k in o:
@@ -463,7 +467,8 @@ def run_ours(args):
                        "partition": "nnz-balanced row blocks, no collective" if not power else
                                     "row blocks + x all-gather per step",
                        "l2": "inputs (%.1f GB) larger than L2; no flush" % (b_alg(nnz, rows, cols) / 1e9),
-                       "slabs": m["slabs"], "persist_window": not args.no_persist, "setup_s": round(m["setup_s"], 2),
+                       "slabs": m["slabs"], "persist_window": m["persist_window"], "persist_window_how": "measured at setup (kept unless off is > 1 % faster)",
+                       "slab_kernels": m["slab_kernels"], "setup_measurements_ms": m["tune_ms"], "setup_s": round(m["setup_s"], 2),
                        "setup_amortised_over_steps": int(round(m["setup_s"] / (t_dev / args.steps))), **m.get("step_stats", {}),
                        **({k: m[k] for k in ("x_exchange_ms_last_step", "exchange") if k in m}),
                        **({"norm_after_last_step": m["last_norm"]} if power else {}),
