@@ -258,6 +258,8 @@ class Job:
             eng.set_option("own_slabs", 1)
         if args.prefetch_x is not None:
             eng.set_option("prefetch_x", args.prefetch_x)
+        if args.persist is not None:
+            eng.set_option("persist", args.persist)
         if exchange in ("pull", "overlap", "packed") and self.world > 1 and shard and not args.shard:
             # slabs aligned with the ranks' x blocks: the exchange of the other blocks runs under the own-block slabs
             eng.set_option("own_slabs", args.own_layout)
@@ -518,6 +520,7 @@ def main():
     ap.add_argument("--graph", type=int, default=None, help="0: do not replay a CUDA graph in exec_device")
     ap.add_argument("--overwrite", action="store_true", help="y = A*x instead of y += A*x")
     ap.add_argument("--no-persist", action="store_true")
+    ap.add_argument("--persist", type=int, default=None, help="L2 window on x: 1 on, 0 off (default: what setup measured)")
     ap.add_argument("--exchange", choices=["pull", "overlap", "nccl", "packed"], default="pull",
                     help="power iteration over several GPUs: how the replicated x is refreshed (DESIGN.md section 7)")
     ap.add_argument("--pull-streams", type=int, default=0)

@@ -968,8 +968,12 @@ int b2_tune_slab_kernels(b200spmv_ctx *ctx)
         B2_CHECK(ctx, cudaEventCreate(&e1));
         float t[2] = {1e30f, 1e30f};
         int rc = 0;
-        for (int round = 0; round < 4 && !rc; round++) {  // on, off, on, off: the best of two tries each
-            const int on = 1 - (round & 1);
+        // OFF first: lines the window has marked persisting stay in the set-aside after it is switched off, so an
+        // "off" measured after an "on" still runs with x pinned (on a rank's block of the 8-way split that hid a 9 %
+        // difference); between the tries the persisting lines are dropped
+        for (int round = 0; round < 4 && !rc; round++) {  // off, on, off, on: the best of two tries each
+            const int on = round & 1;
+            if (!on) { cudaStreamSynchronize(s); cudaCtxResetPersistingL2Cache(); }
             ctx->tune_persist = on;
             ctx->tune_force = 1;
             rc = b2_spmv_launch(ctx, B200SPMV_ACCUMULATE, s);
@@ -986,6 +990,7 @@ int b2_tune_slab_kernels(b200spmv_ctx *ctx)
         cudaEventDestroy(e1);
         if (rc) return rc;
         ctx->persist_tuned = !(t[0] < 0.99f * t[1]);
+        if (!ctx->persist_tuned) { cudaStreamSynchronize(s); cudaCtxResetPersistingL2Cache(); }
         ran_persist = true;
     }
     if (!ctx->tune_mask || ctx->opt_dcsr_x16 >= 0) {  // no slab to measure / a fixed rule was asked for
@@ -1053,6 +1058,8 @@ int b2_spmv_prepare(b200spmv_ctx *ctx, int flags, cudaStream_t s)
     const bool persist = want_persist(ctx, flags);
     if (persist != ctx->persist_set) {
         B2_TRY(set_persist_window(ctx, s, ctx->d_x, (size_t)ctx->cols * 8, persist));
+        // switching the window off must also give the set-aside back (lines marked persisting outlive the window)
+        if (!persist && ctx->persist_set) { cudaStreamSynchronize(s); cudaCtxResetPersistingL2Cache(); }
         ctx->persist_set = persist;
     }
     return 0;
