@@ -134,6 +134,23 @@ B200SPMV_API int b200spmv_exec(b200spmv_ctx *ctx, const void *x_host, void *y_ho
  * receives CUDA-event times of each SpMV (all its kernels), on the launching stream. */
 B200SPMV_API int b200spmv_exec_device(b200spmv_ctx *ctx, int iters, int flags, float *ms_each);
 
+/* The SpMV for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * y = A*x (flags 0) or y += A*x (B200SPMV_ACCUMULATE) on DEVICE vectors the caller passes -- x_dev: cols elements,
+ * y_dev: rows elements (a rank of a row-block split writes its own rows only) -- with the matrix the context was set
+ * up with, kernel 3 (flagged segmented sum) on every column slab, launched on `stream` (a cudaStream_t; NULL = the
+ * context's own stream, and then the call also waits for it).  The call makes no cudaMalloc / cudaFree and creates no
+ * stream, event or graph: the per-tile carries, which setup normally allocates, live in a static device array inside
+ * the library instead (3 MB per GPU that loads the library, held until the process exits).
+ * Limit: every column slab of the matrix must have at most 2^18 tiles of 2048 entries (2^29 stored entries per slab);
+ * larger matrices get B200SPMV_EINVAL with the slab and its tile count in b200spmv_last_error.  Other flags are
+ * rejected (no strict order, no L2 window on the caller's x).
+ * The scratch is shared by every call on the same GPU and keeps the last call's contents (nothing in it has to start
+ * at zero: each tile's carry is written before it is read): calls whose kernels OVERLAP on one GPU -- different
+ * streams, different contexts -- race; calls ordered on one stream do not.  fp64 results equal b200spmv_exec_device's
+ * with kernel 3 bit for bit (same kernel, same tiles). */
+B200SPMV_API int b200spmv_exec_noalloc(b200spmv_ctx *ctx, const void *x_dev, void *y_dev, int flags, void *stream);
+
 B200SPMV_API int b200spmv_set_x(b200spmv_ctx *ctx, const void *x_host);          /* cols elements */
 B200SPMV_API int b200spmv_set_y(b200spmv_ctx *ctx, const void *y_host);          /* rows elements (full) */
 B200SPMV_API int b200spmv_fill_x_synthetic(b200spmv_ctx *ctx, uint64_t seed);    /* synth_x_bits(seed, i) */

@@ -23,6 +23,7 @@ EXPORTS = [
     "b200spmv_get_x", "b200spmv_get_y", "b200spmv_get_csr", "b200spmv_get_csc", "b200spmv_stat_u64",
     "b200spmv_comm_unique_id", "b200spmv_comm_init", "b200spmv_power_iterate",
     "b200spmv_check_synthetic_u64", "b200spmv_mark_row_starts", "b200spmv_max_alive", "b200spmv_max_col_span", "b200spmv_vector_cache_model",
+    "b200spmv_exec_noalloc",
 ]
 
 _lib = None
@@ -122,6 +123,11 @@ class Engine:
         ms = np.zeros(iters, dtype=np.float32)
         self._ck(self.L.b200spmv_exec_device(self.ctx, C.c_int(iters), C.c_int(flags), _p(ms)), "exec_device")
         return ms
+
+    def exec_noalloc(self, x_dev_ptr, y_dev_ptr, flags=0, stream=None):
+        """y (+)= A*x on device vectors given by address (ints), without any allocation inside the library"""
+        self._ck(self.L.b200spmv_exec_noalloc(self.ctx, C.c_void_p(x_dev_ptr), C.c_void_p(y_dev_ptr), C.c_int(flags),
+                                              C.c_void_p(stream)), "exec_noalloc")
 
     def set_x(self, x):
         self._ck(self.L.b200spmv_set_x(self.ctx, _p(np.ascontiguousarray(x))), "set_x")

@@ -165,6 +165,7 @@ struct b200spmv_ctx {
     void *reg_ptr[2] = {nullptr, nullptr};
     size_t reg_bytes[2] = {0, 0};
     bool persist_set = false;
+    void *noalloc_scratch = nullptr;   // device address of spmv.cu's static carry scratch on this context's GPU (b200spmv_exec_noalloc)
     bool persist_tuned = true;    // what b2_tune_slab_kernels measured (window on unless off is > 1 % faster)
     int tune_persist = -1;        // during that measurement: 0 / 1 = force
 

@@ -628,6 +628,30 @@ __global__ void chunk_rows_kernel(const uint32_t *__restrict__ tile_seg, const u
 
 // Flagged format for kernels 3 and 6 (needs bit 31 of the column ids free; otherwise only the row-sequential
 // kernel runs).
+// ---- b200spmv_exec_noalloc: carry scratch that is never allocated ---------------------------------
+// The tile carries of kernel 3 (one row id + one partial sum per 2048-entry tile) normally live in arrays that
+// setup cudaMalloc's.  For callers that must not allocate, the same kernel can write them into this file-scope
+// array instead: NOALLOC_MAX_TILES carry values (8 B each) followed by as many carry rows (4 B each) = 3 MB that
+// every GPU which loads the library holds until the process exits.  In HOST code the name below is only a
+// stand-in for the symbol, not a device address; the address is asked for once per device at setup
+// (noalloc_scratch_address, called from b2_build_flags with the context's device current).
+constexpr uint32_t NOALLOC_MAX_TILES = 1u << 18;  // per column slab: 2^18 tiles x 2048 = 2^29 stored entries
+static __device__ __align__(256) unsigned char g_noalloc_scratch[(size_t)NOALLOC_MAX_TILES * 12];
+static void *g_noalloc_addr[64] = {nullptr};      // by device ordinal
+
+static int noalloc_scratch_address(b200spmv_ctx *ctx)
+{
+    const int dev = ctx->device;
+    void *p = (dev >= 0 && dev < 64) ? g_noalloc_addr[dev] : nullptr;
+    if (!p) {
+        B2_CHECK(ctx, cudaSetDevice(dev));
+        B2_CHECK(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (dev >= 0 && dev < 64) g_noalloc_addr[dev] = p;
+    }
+    ctx->noalloc_scratch = p;
+    return 0;
+}
+
 int b2_build_flags(b200spmv_ctx *ctx)
 {
     DeviceCsr &m = ctx->csr;
@@ -697,6 +721,7 @@ int b2_build_flags(b200spmv_ctx *ctx)
     }
     cudaFree(segidx);
     if (rc) return rc;
+    B2_TRY(noalloc_scratch_address(ctx));
     ctx->flagged = true;
     ctx->colmask = 0x7FFFFFFFu;
     return 0;
@@ -1070,4 +1095,66 @@ int b2_spmv_launch(b200spmv_ctx *ctx, int flags, cudaStream_t s)
     B2_TRY(b2_spmv_prepare(ctx, flags, s));
     return ctx->dtype == B200SPMV_F64 ? launch_dtype<B200SPMV_F64>(ctx, flags, s)
                                       : launch_dtype<B200SPMV_U64>(ctx, flags, s);
+}
+
+// ---- the no-allocation entry point (no counterpart in the reference) --
+// y = A*x or y += A*x on DEVICE vectors the caller passes, with kernel 3 on every column slab and the tile carries in
+// the static scratch above: no cudaMalloc, no cudaFree, no event or stream creation, no stream attribute -- only
+// kernel launches (and one memset of y for y = A*x on a matrix with empty rows) on the given stream.  The matrix is
+// the one the context was set up with.  The kernel writes every tile's carry before the fix-up reads it, so nothing
+// in the scratch has to start at zero; it keeps the last call's carries.  All calls on one GPU share the scratch:
+// two calls whose kernels overlap on the GPU (different streams, different contexts) race.
+template <int DT>
+static int launch_noalloc(b200spmv_ctx *ctx, const uint64_t *x, uint64_t *yfull, int flags, cudaStream_t s)
+{
+    const DeviceCsr &m = ctx->csr;
+    const uint32_t rows = ctx->local_rows;
+    if (rows == 0) return 0;
+    uint64_t *y = yfull + ctx->row_begin;
+    uint64_t *cval = (uint64_t *)ctx->noalloc_scratch;
+    uint32_t *crow = (uint32_t *)((unsigned char *)ctx->noalloc_scratch + (size_t)NOALLOC_MAX_TILES * 8);
+    const size_t stride = ctx->rowptr_stride;
+    for (int sl = 0; sl < ctx->slabs; sl++) {
+        const uint32_t tb = ctx->h_ftile_base[sl], nt = ctx->h_ftile_base[sl + 1] - tb;
+        const bool read_y = (flags & B200SPMV_ACCUMULATE) || sl > 0;
+        const bool has_empty = ctx->h_nseg[sl] < rows;
+        if (!read_y && has_empty) B2_CHECK(ctx, cudaMemsetAsync(y, 0, (size_t)rows * 8, s));  // rows no flag will touch
+        if (nt == 0) continue;
+        const uint32_t *ci = m.colind + ctx->h_slab_off[sl];
+        const uint64_t *va = (const uint64_t *)m.vals + ctx->h_slab_off[sl];
+        const uint32_t *segrow = m.seg_row + sl * stride, *tseg = m.tile_seg + tb + sl;
+#define B2_CALL_NOALLOC(P, R, E) \
+    spmv_flag_kernel<DT, P, R, E, 8><<<nt, B2_FLAG_TILE / 8, 0, s>>>(ci, va, x, y, segrow, rows, tseg, crow, cval, 0u)
+        B2_DISPATCH3(false, read_y, has_empty, B2_CALL_NOALLOC);
+#undef B2_CALL_NOALLOC
+        spmv_fixup_kernel<DT><<<b2_div_up(nt, 256), 256, 0, s>>>(crow, cval, nt, y);
+        B2_CHECK(ctx, cudaGetLastError());
+    }
+    return 0;
+}
+
+extern "C" int b200spmv_exec_noalloc(b200spmv_ctx *ctx, const void *x_dev, void *y_dev, int flags, void *stream)
+{
+    if (!ctx) return B200SPMV_EINVAL;
+    if (!ctx->ready) return b2_fail(ctx, B200SPMV_ESTATE, "exec_noalloc before setup");
+    if (!x_dev || !y_dev) return b2_fail(ctx, B200SPMV_EINVAL, "null vector");
+    if (flags & ~B200SPMV_ACCUMULATE) return b2_fail(ctx, B200SPMV_EINVAL, "exec_noalloc takes B200SPMV_ACCUMULATE or 0");
+    if (!ctx->flagged || !ctx->noalloc_scratch) return b2_fail(ctx, B200SPMV_ESTATE, "exec_noalloc needs the flagged layout");
+    for (int sl = 0; sl < ctx->slabs; sl++) {
+        const uint32_t nt = ctx->h_ftile_base[sl + 1] - ctx->h_ftile_base[sl];
+        if (nt > NOALLOC_MAX_TILES) {
+            char buf[200];
+            snprintf(buf, sizeof buf, "exec_noalloc: column slab %d has %u tiles of 2048 entries, the static scratch holds %u (2^29 entries per slab)",
+                     sl, nt, NOALLOC_MAX_TILES);
+            ctx->err = buf;
+            return B200SPMV_EINVAL;
+        }
+    }
+    B2_CHECK(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    const int rc = ctx->dtype == B200SPMV_F64 ? launch_noalloc<B200SPMV_F64>(ctx, (const uint64_t *)x_dev, (uint64_t *)y_dev, flags, s)
+                                              : launch_noalloc<B200SPMV_U64>(ctx, (const uint64_t *)x_dev, (uint64_t *)y_dev, flags, s);
+    if (rc) return rc;
+    if (!stream) B2_CHECK(ctx, cudaStreamSynchronize(s));  // the caller's own stream is the caller's to wait on
+    return 0;
 }
