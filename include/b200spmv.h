@@ -65,7 +65,9 @@ B200SPMV_API void b200spmv_destroy(b200spmv_ctx *ctx);
 B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx may be NULL: last create error */
 
 /* Tunables, set before setup: "slabs" (column slabs, 0 = auto), "persist_bytes"
- * (L2 set-aside cap, 0 = device max), "require_aligned" (1 = enforce the 64-byte rule),
+ * (L2 set-aside cap, 0 = device max), "persist" (the L2 access-policy window + evict_last hint on x: -1, the default =
+ * kept unless setup measured that dropping it is more than 1 % faster; 0 = off; 1 = on; stat "persist" tells which is
+ * in force; flag B200SPMV_NO_PERSIST drops it for one call), "require_aligned" (1 = enforce the 64-byte rule),
  * "keep_csc" (1 = keep the device CSC copy for b200spmv_get_csc), "profile", "kernel" (3 = flagged
  * segmented sum with one tile per CTA, the default; 6 = the same by persistent warps, with its tuning knobs
  * "stream_db", "stream_pf", "stream_occ", "stream_vchunks"), "world" then "rank" (take the
