@@ -92,10 +92,13 @@ __device__ __forceinline__ void store_segment(uint64_t *__restrict__ y, const ui
         y[row] = v;
     }
 }
+#ifndef B2_K3_CTAS
+#define B2_K3_CTAS 4  // CTAs per SM the register budget is cut for (measurement builds: make variant DEFS=-DB2_K3_CTAS=5)
+#endif
 // EPT = consecutive entries per thread (8 or 16); the tile is always B2_FLAG_TILE entries, so the
 // CTA has B2_FLAG_TILE / EPT threads.
 template <int DT, bool PERSIST, bool READ_Y, bool HAS_EMPTY, int EPT>
-__global__ void __launch_bounds__(B2_FLAG_TILE / EPT, EPT == 8 ? 4 : 4)
+__global__ void __launch_bounds__(B2_FLAG_TILE / EPT, B2_K3_CTAS)
 spmv_flag_kernel(const uint32_t *__restrict__ colind, const uint64_t *__restrict__ vals,
                  const uint64_t *__restrict__ x, uint64_t *__restrict__ y,
                  const uint32_t *__restrict__ seg_row, uint32_t rows, const uint32_t *__restrict__ tile_seg,
