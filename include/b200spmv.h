@@ -64,7 +64,8 @@ B200SPMV_API int b200spmv_create(b200spmv_ctx **out, int device);
 B200SPMV_API void b200spmv_destroy(b200spmv_ctx *ctx);
 B200SPMV_API const char *b200spmv_last_error(const b200spmv_ctx *ctx); /* ctx may be NULL: last create error */
 
-/* Tunables, set before setup: "slabs" (column slabs, 0 = auto), "persist_bytes"
+/* Tunables, set before setup: "slabs" (column slabs, 0 = auto: sized so that a slab's slice of x fits L2, capped by the
+ * entries per row and slab, 1 for a matrix whose entries sit within a narrow band around the diagonal -- stat "band_nz"), "persist_bytes"
  * (L2 set-aside cap, 0 = device max), "persist" (the L2 access-policy window + evict_last hint on x: -1, the default =
  * kept unless setup measured that dropping it is more than 1 % faster; 0 = off; 1 = on; stat "persist" tells which is
  * in force; flag B200SPMV_NO_PERSIST drops it for one call), "require_aligned" (1 = enforce the 64-byte rule),

@@ -82,6 +82,7 @@ struct b200spmv_ctx {
     uint64_t local_nnz = 0;
     uint64_t nonempty_rows = 0;   // of this rank's block
     uint64_t upper_half_nnz = 0;  // entries of the block in columns >= cols/2 (column skew, choose_slabs)
+    uint64_t band_nnz = 0;        // entries of the block within L2/16 worth of columns of the diagonal (choose_slabs)
     int slabs = 1;
     uint32_t slab_cols = 0;       // columns per slab (last may be short) when the slabs are uniform
     uint32_t h_slab_col[65] = {0};     // column boundaries of the slabs
@@ -248,6 +249,8 @@ int b2_compress(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *k
                 const uint32_t *src_other, const void *src_vals, uint32_t *dst_ptr, uint32_t dst_ptr_add,
                 uint32_t *dst_ind, void *dst_vals, cudaStream_t s);
 int b2_add_u32(b200spmv_ctx *ctx, uint32_t *a, uint64_t n, uint32_t add, cudaStream_t s);
+int b2_count_band(b200spmv_ctx *ctx, const uint32_t *colptr, const uint32_t *rowind, uint32_t mask, uint32_t cols, uint32_t rows,
+                  uint32_t window, uint64_t *out, cudaStream_t s);
 int b2_validate_indices(b200spmv_ctx *ctx, const uint32_t *d_ind, uint64_t n, uint32_t mask, uint32_t limit,
                         const uint32_t *d_ptr, uint64_t nptr, cudaStream_t s);
 int b2_count_nonempty(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint32_t *key, uint32_t key_mask,

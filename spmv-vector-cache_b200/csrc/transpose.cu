@@ -140,6 +140,47 @@ int b2_count_nonempty(b200spmv_ctx *ctx, uint32_t nkeys, uint64_t n, const uint3
     return rc;
 }
 
+// Entries (r, c) of a CSC block whose column lies within `window` columns of the row's place on the diagonal
+// (r * cols / rows): a row-ordered sweep gathers those from a slice of x that moves with it and stays in L2 whatever
+// the size of x.  One warp per column (grid-stride), lanes over the column's entries.
+__global__ void __launch_bounds__(256) band_count_kernel(const uint32_t *__restrict__ colptr, const uint32_t *__restrict__ rowind,
+                                                         uint32_t mask, uint32_t cols, uint32_t rows, uint32_t window,
+                                                         unsigned long long *__restrict__ out)
+{
+    const uint32_t lane = threadIdx.x & 31, nwarps = gridDim.x * (blockDim.x >> 5);
+    unsigned long long mine = 0;
+    for (uint32_t c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < cols; c += nwarps) {
+        const uint32_t b = colptr[c], e = colptr[c + 1];
+        for (uint32_t i = b + lane; i < e; i += 32) {
+            const uint64_t d = (uint64_t)(rowind[i] & mask) * cols / rows;
+            const uint64_t dist = d > c ? d - c : c - d;
+            mine += dist <= window;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) mine += __shfl_down_sync(0xffffffffu, mine, o);
+    if (lane == 0 && mine) atomicAdd(out, mine);
+}
+
+int b2_count_band(b200spmv_ctx *ctx, const uint32_t *colptr, const uint32_t *rowind, uint32_t mask, uint32_t cols, uint32_t rows,
+                  uint32_t window, uint64_t *out, cudaStream_t s)
+{
+    *out = 0;
+    if (cols == 0 || rows == 0) return 0;
+    unsigned long long *cnt = nullptr;
+    B2_TRY(b2_alloc(ctx, &cnt, 1));
+    int rc = 0;
+    cudaError_t e = cudaMemsetAsync(cnt, 0, 8, s);
+    band_count_kernel<<<(unsigned)ctx->sms * 8, 256, 0, s>>>(colptr, rowind, mask, cols, rows, window, cnt);
+    unsigned long long h = 0;
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&h, cnt, 8, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) { ctx->err = cudaGetErrorString(e); ctx->cuda_error = (int)e; rc = B200SPMV_ECUDA; }
+    b2_free(cnt);
+    *out = h;
+    return rc;
+}
+
 int b2_add_u32(b200spmv_ctx *ctx, uint32_t *a, uint64_t n, uint32_t add, cudaStream_t s)
 {
     if (n == 0 || add == 0) return 0;

@@ -61,7 +61,8 @@ def test_bench_lines_under_profiles_carry_the_contract_keys():
     need = {"metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
             "dtype", "data", "config", "roofline", "e2e", "gpu_launches", "clocks"}
     for name in ("r01_bench_default.json", "r01_bench_8gpu.json", "r01_bench_8gpu_rmat.json", "r01_bench_8gpu_power_pull.json",
-                 "r02_bench_1gpu.json", "r02_bench_2gpu.json", "r02_bench_4gpu.json", "r02_bench_8gpu.json"):
+                 "r02_bench_1gpu.json", "r02_bench_2gpu.json", "r02_bench_4gpu.json", "r02_bench_8gpu.json",
+                 "r02_bench_1gpu_band.json", "r02_bench_1gpu_banded.json"):
         d = json.loads(open(os.path.join(PROF, name)).read().strip().splitlines()[-1])
         assert need <= set(d), (name, need - set(d))
         assert set(d["roofline"]) >= {"bound", "achieved", "peak", "unit", "frac", "traffic"}
@@ -86,3 +87,10 @@ def test_round2_bench_lines_carry_parity_and_the_other_configs():
         vals[n] = (d["value"], oc["rmat"]["value"], oc[power[-1]]["value"], d["e2e"]["value"])
     assert vals[8][0] / vals[1][0] >= 6 and vals[8][1] / vals[1][1] >= 6 and vals[8][2] / vals[1][2] >= 6
     assert vals[8][3] > 2 * vals[1][3]  # end to end now scales (each rank uploads 1/N of x)
+
+
+def test_band_workload_is_hbm_bound_and_one_slab():
+    """pure band at >= 0.70 of the measured HBM peak; setup recognises the band and does not cut it"""
+    d = json.loads(open(os.path.join(PROF, "r02_bench_1gpu_band.json")).read().strip().splitlines()[-1])
+    assert d["config"]["slabs"] == 1 and d["roofline"]["frac"] >= 0.70 and d["parity"]["ok"] is True
+    assert d["roofline"]["traffic"] is not None and d["roofline"]["traffic"] < 1.1 * d["roofline"]["algorithmic_bytes_per_step"]
