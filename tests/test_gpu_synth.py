@@ -343,3 +343,18 @@ def test_largest_configs_full_size_parity(b2, oracle, config):
             e.set_x(e.get_y())
         assert xp.tobytes() == e.get_x().tobytes()
     e.close()
+
+
+def test_band_matrix_is_not_cut_into_slabs(b2):
+    """a matrix banded around the diagonal keeps one column slab however large x is (its gathers follow the row sweep);
+    the same size with random entries is cut (api.cu choose_slabs, transpose.cu b2_count_band)"""
+    rows = 1 << 24  # x = 134 MB > L2
+    e = b2.Engine(0)
+    e.setup_synthetic(b2.SYNTH_BAND, rows, rows, 16, SEED, b2.U64)
+    assert e.stat("band_nz") == e.stat("nz") and e.stat("slabs") == 1
+    e.close()
+    e = b2.Engine(0)
+    e.setup_synthetic(2, rows, rows, 5, SEED, b2.U64)  # banded(11) + 5 random per row
+    nz, band = e.stat("nz"), e.stat("band_nz")
+    assert 0.68 * nz < band < 0.80 * nz and e.stat("slabs") > 1
+    e.close()
