@@ -282,6 +282,9 @@ ORACLE_API void oracle_power_iterate_u64(uint32_t n, const uint32_t *colptr,
 /* of the valid lines :208-231.  Sequential, one access after the other.      */
 /* out[7]: reads, readMisses, conflictEvictions, coldMissSkips, ddrReads,     */
 /* flushWrites, hits.                                                         */
+/* PARITY UNPINNED: the reference ships no counter fixtures for this cache    */
+/* and its Chisel simulator cannot run here (no Scala toolchain); this is a   */
+/* reading of the RTL's state machine, checked against nothing but itself.    */
 /* ------------------------------------------------------------------------- */
 ORACLE_API void oracle_vector_cache_model(uint32_t nnz, const uint32_t *inds, int depth_log2, int cms, uint64_t *out)
 {

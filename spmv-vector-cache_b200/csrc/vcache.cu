@@ -8,6 +8,8 @@
 // eviction, :264-268); with cold-miss skip the first touch of a row (bit 31 of the index, set by
 // SparseMatrix::markRowStarts) does not read DRAM (:240-252); the flush phase writes every valid line
 // back (:208-231).  The counters are the ones software/HardwareSpMVNewCache.cpp:189-204 reports.
+// Parity unpinned: the reference holds no counter fixtures and its simulator cannot run here; the tests compare this
+// parallel form with a sequential restatement of the same reading of the RTL (oracle_vector_cache_model), not with the RTL.
 //
 // A direct-mapped cache is independent per set, so the sequential simulation parallelises: stable radix
 // sort of the row-index stream by set (sort.cu), then an access misses iff it is the first of its set or
